@@ -1,0 +1,690 @@
+// libdpk: C ABI (include/dpk.h) over the kernels in dpk_kernels.cuh.
+// Host code here only validates, plans (tiles, buckets) and enqueues.
+#include <dlfcn.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <algorithm>
+#include <new>
+
+#include "dpk_internal.h"
+
+namespace dpk {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return (int)e;
+}
+
+int nccl_fail(ncclResult_t r, const char* what) {
+  const NcclApi* api = nccl_api();
+  set_error("NCCL error %d (%s) in %s", (int)r,
+            (api && api->GetErrorString) ? api->GetErrorString(r) : "?", what);
+  return DPK_E_NCCL;
+}
+
+const NcclApi* nccl_api() {
+  static NcclApi api;
+  static std::once_flag once;
+  static char why[256] = "";
+  std::call_once(once, [] {
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) {
+      snprintf(why, sizeof(why), "dlopen(libnccl.so.2) failed: %s", dlerror());
+      return;
+    }
+    bool all = true;
+#define BIND(field, sym)                                         \
+  do {                                                           \
+    *(void**)(&api.field) = dlsym(lib, sym);                     \
+    if (!api.field) { all = false; snprintf(why, sizeof(why), "missing NCCL symbol %s", sym); } \
+  } while (0)
+    BIND(GetUniqueId, "ncclGetUniqueId");
+    BIND(CommInitRank, "ncclCommInitRank");
+    BIND(CommDestroy, "ncclCommDestroy");
+    BIND(CommAbort, "ncclCommAbort");
+    BIND(AllReduce, "ncclAllReduce");
+    BIND(AllGather, "ncclAllGather");
+    BIND(Broadcast, "ncclBroadcast");
+    BIND(GroupStart, "ncclGroupStart");
+    BIND(GroupEnd, "ncclGroupEnd");
+    BIND(CommGetAsyncError, "ncclCommGetAsyncError");
+    BIND(GetErrorString, "ncclGetErrorString");
+#undef BIND
+    api.ok = all;
+  });
+  if (!api.ok) {
+    set_error("NCCL unavailable: %s", why);
+    return nullptr;
+  }
+  return &api;
+}
+
+static inline int elem_size(int dtype) { return dtype == DPK_F32 ? 4 : 2; }
+static inline int vec_elems(int dtype) { return 16 / elem_size(dtype); }
+
+// RAII: make the handle's device current for the duration of a call.
+struct DeviceGuard {
+  int prev = -1;
+  bool switched = false;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) {
+      err = cudaSetDevice(dev);
+      switched = (err == cudaSuccess);
+    }
+  }
+  ~DeviceGuard() {
+    if (switched) cudaSetDevice(prev);
+  }
+};
+#define DPK_GUARD(h)                       \
+  ::dpk::DeviceGuard guard__((h)->device); \
+  if (guard__.err != cudaSuccess) return ::dpk::cuda_fail(guard__.err, "cudaSetDevice")
+
+template <typename Kern>
+static int grid_for(Kern kern, int n_work, int sm_count, int* out) {
+  int occ = 0;
+  DPK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, 0));
+  if (occ < 1) occ = 1;
+  long long g = (long long)occ * sm_count;
+  if (g > n_work) g = n_work;
+  if (g < 1) g = 1;
+  *out = (int)g;
+  return 0;
+}
+
+// Optional CUDA-event bracket around one streaming kernel (bench instrumentation).
+struct KernelTimer {
+  dpk_handle* h;
+  int which;
+  cudaStream_t st;
+  cudaEvent_t end = nullptr;
+  KernelTimer(dpk_handle* h_, int which_, cudaStream_t st_) : h(h_), which(which_), st(st_) {
+    if (!h->timing || h->tcount[which] >= DPK_TIMING_SLOTS) return;
+    auto& v = h->tev[which];
+    const size_t need = 2 * (size_t)(h->tcount[which] + 1);
+    while (v.size() < need) {
+      cudaEvent_t e = nullptr;
+      if (cudaEventCreate(&e) != cudaSuccess) return;
+      v.push_back(e);
+    }
+    cudaEventRecord(v[need - 2], st);
+    end = v[need - 1];
+  }
+  ~KernelTimer() {
+    if (end) {
+      cudaEventRecord(end, st);
+      h->tcount[which]++;
+    }
+  }
+};
+
+// ---- pass 1 ---------------------------------------------------------------
+
+template <typename T>
+static int launch_sumsq(dpk_handle* h, int tile_begin, int tile_end, float inv_scale,
+                        cudaStream_t st) {
+  const int n = tile_end - tile_begin;
+  if (n <= 0) return 0;
+  auto kern = sumsq_tiles_kernel<T, 4>;
+  int grid = 0;
+  if (int rc = grid_for(kern, n, h->sm_count, &grid)) return rc;
+  {
+    KernelTimer timer(h, 1, st);
+    kern<<<grid, kThreads, 0, st>>>((const T*)h->g, h->d_tiles, tile_begin, tile_end, inv_scale,
+                                    h->d_partials_pre);
+  }
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int launch_segment_reduce(dpk_handle* h, const TilePartial* partials, cudaStream_t st) {
+  if (h->n_seg == 0) return 0;
+  const int grid = std::min(h->n_seg, 4 * h->sm_count);
+  segment_reduce_kernel<<<grid, kThreads, 0, st>>>(partials, h->d_seg_tile_begin, h->d_seg_sumsq,
+                                                   h->d_seg_bad, h->n_seg);
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- pass 2 ---------------------------------------------------------------
+
+template <typename T, int K, int GM>
+static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef, int skip,
+                              cudaStream_t st) {
+  const int n_tiles = (int)h->tiles.size();
+  if (n_tiles == 0) return 0;
+  UpdateArgs<T, K> a;
+  a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
+  for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
+  a.tiles = h->d_tiles;
+  a.n_tiles = n_tiles;
+  a.partials = h->d_partials_post;
+  a.results = h->d_results;
+  a.use_clip_coef = use_coef;
+  a.skip_if_nonfinite = skip;
+  a.s = sc;
+  auto kern = fused_update_kernel<T, K, GM, 2>;
+  int grid = 0;
+  if (int rc = grid_for(kern, n_tiles, h->sm_count, &grid)) return rc;
+  {
+    KernelTimer timer(h, 0, st);
+    kern<<<grid, kThreads, 0, st>>>(a);
+  }
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <typename T, int K>
+static int launch_update_gm(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int gm,
+                            cudaStream_t st) {
+  switch (gm) {
+    case DPK_GRAD_KEEP: return launch_update_impl<T, K, DPK_GRAD_KEEP>(h, sc, use_coef, skip, st);
+    case DPK_GRAD_CLIPPED: return launch_update_impl<T, K, DPK_GRAD_CLIPPED>(h, sc, use_coef, skip, st);
+    default: return launch_update_impl<T, K, DPK_GRAD_ZERO>(h, sc, use_coef, skip, st);
+  }
+}
+
+template <typename T>
+static int launch_update(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int gm,
+                         cudaStream_t st) {
+  switch (h->n_ema) {
+    case 0: return launch_update_gm<T, 0>(h, sc, use_coef, skip, gm, st);
+    case 1: return launch_update_gm<T, 1>(h, sc, use_coef, skip, gm, st);
+    case 2: return launch_update_gm<T, 2>(h, sc, use_coef, skip, gm, st);
+    case 3: return launch_update_gm<T, 3>(h, sc, use_coef, skip, gm, st);
+    default: return launch_update_gm<T, 4>(h, sc, use_coef, skip, gm, st);
+  }
+}
+
+static void free_handle(dpk_handle* h) {
+  if (!h) return;
+  if (h->comm) {
+    const NcclApi* api = nccl_api();
+    if (api) api->CommDestroy(h->comm);
+  }
+  if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
+  if (h->ev_ready) cudaEventDestroy(h->ev_ready);
+  if (h->ev_done) cudaEventDestroy(h->ev_done);
+  cudaFree(h->d_tiles);
+  cudaFree(h->d_seg_tile_begin);
+  cudaFree(h->d_partials_pre);
+  cudaFree(h->d_partials_post);
+  cudaFree(h->d_seg_sumsq);
+  cudaFree(h->d_seg_bad);
+  cudaFree(h->d_seg_norms);
+  cudaFree(h->d_results);
+  if (h->h_results_pinned) cudaFreeHost(h->h_results_pinned);
+  for (auto& v : h->tev)
+    for (cudaEvent_t e : v) cudaEventDestroy(e);
+  delete h;
+}
+
+// Device-side scratch, tables, stream and events: created on the first
+// dpk_bind (dpk_create itself is pure host planning and needs no GPU).
+static int ensure_device_state(dpk_handle* h) {
+  if (h->d_results) return 0;
+  DPK_GUARD(h);
+  int sm = 0;
+  DPK_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device));
+  h->sm_count = sm;
+  const size_t nt = std::max<size_t>(h->tiles.size(), 1), ns = std::max(h->n_seg, 1);
+  DPK_CUDA(cudaMalloc(&h->d_tiles, nt * sizeof(Tile)));
+  DPK_CUDA(cudaMalloc(&h->d_seg_tile_begin, (ns + 1) * sizeof(int)));
+  DPK_CUDA(cudaMalloc(&h->d_partials_pre, nt * sizeof(TilePartial)));
+  DPK_CUDA(cudaMalloc(&h->d_partials_post, nt * sizeof(TilePartial)));
+  DPK_CUDA(cudaMalloc(&h->d_seg_sumsq, ns * sizeof(double)));
+  DPK_CUDA(cudaMalloc(&h->d_seg_bad, ns * sizeof(unsigned)));
+  DPK_CUDA(cudaMalloc(&h->d_seg_norms, ns * sizeof(double)));
+  DPK_CUDA(cudaMallocHost(&h->h_results_pinned, DPK_R_COUNT * sizeof(double)));
+  if (!h->tiles.empty())
+    DPK_CUDA(cudaMemcpy(h->d_tiles, h->tiles.data(), h->tiles.size() * sizeof(Tile), cudaMemcpyHostToDevice));
+  DPK_CUDA(cudaMemcpy(h->d_seg_tile_begin, h->seg_tile_begin.data(), (h->n_seg + 1) * sizeof(int),
+                      cudaMemcpyHostToDevice));
+  int lo = 0, hi = 0;
+  DPK_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  DPK_CUDA(cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, hi));
+  DPK_CUDA(cudaEventCreateWithFlags(&h->ev_ready, cudaEventDisableTiming));
+  DPK_CUDA(cudaEventCreateWithFlags(&h->ev_done, cudaEventDisableTiming));
+  // last: d_results doubles as the "initialised" marker
+  double* res = nullptr;
+  DPK_CUDA(cudaMalloc(&res, DPK_R_COUNT * sizeof(double)));
+  const double init[DPK_R_COUNT] = {0, 1.0, 0, 0, 0, 0, 0, 0};
+  cudaError_t e = cudaMemcpy(res, init, sizeof(init), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { cudaFree(res); return cuda_fail(e, "cudaMemcpy results"); }
+  h->d_results = res;
+  return 0;
+}
+
+}  // namespace dpk
+
+using namespace dpk;
+
+extern "C" {
+
+int dpk_abi_version(void) { return DPK_ABI_VERSION; }
+const char* dpk_last_error(void) { return g_err; }
+
+int dpk_create(dpk_handle** out, const dpk_config* cfg) {
+  if (!out || !cfg) { set_error("dpk_create: null argument"); return DPK_E_BADARG; }
+  *out = nullptr;
+  if (cfg->abi_version != DPK_ABI_VERSION) {
+    set_error("dpk_create: abi_version %d, library is %d", cfg->abi_version, DPK_ABI_VERSION);
+    return DPK_E_BADARG;
+  }
+  if (cfg->dtype != DPK_F32 && cfg->dtype != DPK_BF16) {
+    set_error("dpk_create: unknown dtype %d", cfg->dtype);
+    return DPK_E_BADARG;
+  }
+  if (cfg->n_ema < 0 || cfg->n_ema > DPK_MAX_EMA) {
+    set_error("dpk_create: n_ema %d outside 0..%d", cfg->n_ema, DPK_MAX_EMA);
+    return DPK_E_LIMIT;
+  }
+  if (cfg->n_segments < 0 || cfg->n_elems < 0 ||
+      (cfg->n_segments > 0 && (!cfg->seg_offsets || !cfg->seg_numel)) ||
+      (cfg->n_ema > 0 && !cfg->ema_rates)) {
+    set_error("dpk_create: bad segment table or ema_rates");
+    return DPK_E_BADARG;
+  }
+  const int ve = vec_elems(cfg->dtype);
+  int tile_elems = cfg->tile_elems ? cfg->tile_elems : 8192;
+  if (tile_elems < 1024 || tile_elems % 1024 != 0 || tile_elems > (1 << 20)) {
+    set_error("dpk_create: tile_elems %d must be a multiple of 1024 in [1024, 2^20]", tile_elems);
+    return DPK_E_BADARG;
+  }
+  if (cfg->n_elems % ve != 0) {
+    set_error("dpk_create: n_elems %lld is not a whole number of 16-byte vectors", (long long)cfg->n_elems);
+    return DPK_E_BADARG;
+  }
+
+  dpk_handle* h = new (std::nothrow) dpk_handle();
+  if (!h) { set_error("dpk_create: out of host memory"); return DPK_E_NOMEM; }
+  h->dtype = cfg->dtype;
+  h->device = cfg->device;
+  h->n_seg = cfg->n_segments;
+  h->n_ema = cfg->n_ema;
+  h->tile_elems = tile_elems;
+  h->n_elems = cfg->n_elems;
+  h->beta1 = cfg->beta1; h->beta2 = cfg->beta2; h->eps = cfg->eps;
+  for (int k = 0; k < cfg->n_ema; ++k) h->ema_rates[k] = cfg->ema_rates[k];
+
+  // segments: ascending, 16-byte aligned starts, ragged tails stay inside the gap
+  long long prev_end = 0;
+  long long n_tiles_ll = 0;
+  for (int s = 0; s < h->n_seg; ++s) {
+    const long long off = cfg->seg_offsets[s], len = cfg->seg_numel[s];
+    if (off < 0 || len < 0 || off % ve != 0 || off < prev_end) {
+      set_error("dpk_create: segment %d (offset %lld, numel %lld) misaligned or overlapping", s, off, len);
+      delete h;
+      return DPK_E_BADARG;
+    }
+    prev_end = off + (len + ve - 1) / ve * ve;
+    if (prev_end > h->n_elems) {
+      set_error("dpk_create: segment %d ends at %lld past n_elems %lld", s, prev_end, (long long)h->n_elems);
+      delete h;
+      return DPK_E_BADARG;
+    }
+    h->seg_off.push_back(off);
+    h->seg_len.push_back(len);
+    n_tiles_ll += (len + tile_elems - 1) / tile_elems;
+  }
+  if (n_tiles_ll > 0x7fffffffLL / 2) {
+    set_error("dpk_create: %lld tiles; raise tile_elems", n_tiles_ll);
+    delete h;
+    return DPK_E_LIMIT;
+  }
+  h->tiles.reserve((size_t)n_tiles_ll);
+  h->seg_tile_begin.resize(h->n_seg + 1);
+  for (int s = 0; s < h->n_seg; ++s) {
+    h->seg_tile_begin[s] = (int)h->tiles.size();
+    for (long long pos = 0; pos < h->seg_len[s]; pos += tile_elems) {
+      Tile t;
+      t.start = h->seg_off[s] + pos;
+      t.len = (int)std::min<long long>(tile_elems, h->seg_len[s] - pos);
+      t.seg = s;
+      h->tiles.push_back(t);
+    }
+  }
+  h->seg_tile_begin[h->n_seg] = (int)h->tiles.size();
+
+  // buckets: walk tensors from the last (first gradient ready) to the first,
+  // closing a bucket once it reaches the cap -- DDP's rebuilt-bucket policy.
+  {
+    const long long cap = cfg->bucket_cap_bytes > 0 ? cfg->bucket_cap_bytes : (128LL << 20);
+    const int es = elem_size(h->dtype);
+    int seg_end = h->n_seg;
+    long long bytes = 0;
+    for (int s = h->n_seg - 1; s >= 0; --s) {
+      bytes += h->seg_len[s] * es;
+      if (bytes >= cap || s == 0) {
+        Bucket b;
+        b.seg_begin = s;
+        b.seg_end = seg_end;
+        b.start = h->seg_off[s];
+        const long long end = (seg_end == h->n_seg) ? h->n_elems : h->seg_off[seg_end];
+        b.count = end - b.start;
+        b.tile_begin = h->seg_tile_begin[s];
+        b.tile_end = h->seg_tile_begin[seg_end];
+        h->buckets.push_back(b);
+        seg_end = s;
+        bytes = 0;
+      }
+    }
+  }
+
+  *out = h;
+  return 0;
+}
+
+int dpk_destroy(dpk_handle* h) {
+  if (!h) return 0;
+  if (h->d_results || h->comm_stream || h->d_tiles) {
+    DeviceGuard guard(h->device);
+    if (h->comm_stream) cudaStreamSynchronize(h->comm_stream);
+    free_handle(h);
+  } else {
+    free_handle(h);
+  }
+  return 0;
+}
+
+int dpk_bind(dpk_handle* h, void* d_params, void* d_grads, void* d_exp_avg, void* d_exp_avg_sq,
+             void* const* d_emas) {
+  if (!h) { set_error("dpk_bind: null handle"); return DPK_E_BADARG; }
+  void* ptrs[4 + DPK_MAX_EMA] = {d_params, d_grads, d_exp_avg, d_exp_avg_sq};
+  if (h->n_ema > 0 && !d_emas) { set_error("dpk_bind: d_emas is null"); return DPK_E_BADARG; }
+  for (int k = 0; k < h->n_ema; ++k) ptrs[4 + k] = d_emas[k];
+  for (int i = 0; i < 4 + h->n_ema; ++i) {
+    if (h->n_elems > 0 && (!ptrs[i] || ((uintptr_t)ptrs[i] & 15u))) {
+      set_error("dpk_bind: buffer %d is null or not 16-byte aligned", i);
+      return DPK_E_BADARG;
+    }
+    for (int j = 0; j < i; ++j)
+      if (h->n_elems > 0 && ptrs[i] == ptrs[j]) {
+        set_error("dpk_bind: buffers %d and %d alias", j, i);
+        return DPK_E_BADARG;
+      }
+  }
+  if (int rc = ensure_device_state(h)) return rc;
+  h->p = d_params; h->g = d_grads; h->m = d_exp_avg; h->v = d_exp_avg_sq;
+  for (int k = 0; k < h->n_ema; ++k) h->ema[k] = d_emas[k];
+  h->bound = true;
+  return 0;
+}
+
+// ---- communicator -----------------------------------------------------------
+
+int dpk_comm_unique_id(void* out128) {
+  if (!out128) { set_error("dpk_comm_unique_id: null"); return DPK_E_BADARG; }
+  const NcclApi* api = nccl_api();
+  if (!api) return DPK_E_NCCL;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  DPK_NCCL(api->GetUniqueId(&id));
+  memcpy(out128, &id, 128);
+  return 0;
+}
+
+int dpk_comm_init(dpk_handle* h, const void* id128, int32_t world_size, int32_t rank) {
+  if (!h || !id128 || world_size < 1 || rank < 0 || rank >= world_size) {
+    set_error("dpk_comm_init: bad argument");
+    return DPK_E_BADARG;
+  }
+  if (h->comm) { set_error("dpk_comm_init: communicator already initialised"); return DPK_E_STATE; }
+  const NcclApi* api = nccl_api();
+  if (!api) return DPK_E_NCCL;
+  DPK_GUARD(h);
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  DPK_NCCL(api->CommInitRank(&h->comm, world_size, id, rank));
+  h->world = world_size;
+  h->rank = rank;
+  return 0;
+}
+
+int dpk_world_size(const dpk_handle* h) { return h ? h->world : 0; }
+
+int dpk_num_buckets(const dpk_handle* h) { return h ? (int)h->buckets.size() : 0; }
+
+int dpk_bucket_range(const dpk_handle* h, int32_t b, int64_t* start, int64_t* count) {
+  if (!h || b < 0 || b >= (int)h->buckets.size() || !start || !count) {
+    set_error("dpk_bucket_range: bad argument");
+    return DPK_E_BADARG;
+  }
+  *start = h->buckets[b].start;
+  *count = h->buckets[b].count;
+  return 0;
+}
+
+int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream) {
+  if (!h || b < 0 || b >= (int)h->buckets.size()) { set_error("dpk_bucket_ready: bad bucket"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_bucket_ready: buffers not bound"); return DPK_E_STATE; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  if (h->world <= 1) return 0;  // single replica: nothing to exchange
+  const NcclApi* api = nccl_api();
+  if (!api || !h->comm) { set_error("dpk_bucket_ready: communicator not initialised"); return DPK_E_STATE; }
+  const Bucket& bk = h->buckets[b];
+  DPK_CUDA(cudaEventRecord(h->ev_ready, (cudaStream_t)producer_stream));
+  DPK_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_ready, 0));
+  char* base = (char*)h->g + bk.start * elem_size(h->dtype);
+  // ncclAvg pre-multiplies each rank's contribution by 1/W and sums: the
+  // reducer's semantics, in place, no copy-in / copy-out.
+  DPK_NCCL(api->AllReduce(base, base, (size_t)bk.count, h->dtype == DPK_F32 ? ncclFloat32 : ncclBfloat16,
+                          ncclAvg, h->comm, h->comm_stream));
+  DPK_CUDA(cudaEventRecord(h->ev_done, h->comm_stream));
+  h->any_enqueued = true;
+  return 0;
+}
+
+int dpk_wait_allreduce(dpk_handle* h, void* consumer_stream) {
+  if (!h) { set_error("dpk_wait_allreduce: null handle"); return DPK_E_BADARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  if (h->any_enqueued) {
+    DPK_CUDA(cudaStreamWaitEvent((cudaStream_t)consumer_stream, h->ev_done, 0));
+    h->any_enqueued = false;
+    if (h->comm) {
+      const NcclApi* api = nccl_api();
+      ncclResult_t async = ncclSuccess;
+      if (api && api->CommGetAsyncError(h->comm, &async) == ncclSuccess && async != ncclSuccess &&
+          async != ncclInProgress)
+        return nccl_fail(async, "asynchronous NCCL error");
+    }
+  }
+  return 0;
+}
+
+int dpk_broadcast_state(dpk_handle* h, int32_t root, int32_t include_ema, void* stream) {
+  if (!h) { set_error("dpk_broadcast_state: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_broadcast_state: buffers not bound"); return DPK_E_STATE; }
+  if (h->world <= 1) return 0;
+  if (root < 0 || root >= h->world) { set_error("dpk_broadcast_state: bad root"); return DPK_E_BADARG; }
+  const NcclApi* api = nccl_api();
+  if (!api || !h->comm) { set_error("dpk_broadcast_state: communicator not initialised"); return DPK_E_STATE; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  const ncclDataType_t dt = h->dtype == DPK_F32 ? ncclFloat32 : ncclBfloat16;
+  DPK_NCCL(api->GroupStart());
+  ncclResult_t r = api->Broadcast(h->p, h->p, (size_t)h->n_elems, dt, root, h->comm, (cudaStream_t)stream);
+  for (int k = 0; r == ncclSuccess && include_ema && k < h->n_ema; ++k)
+    r = api->Broadcast(h->ema[k], h->ema[k], (size_t)h->n_elems, dt, root, h->comm, (cudaStream_t)stream);
+  ncclResult_t r2 = api->GroupEnd();
+  if (r != ncclSuccess) return nccl_fail(r, "ncclBroadcast");
+  if (r2 != ncclSuccess) return nccl_fail(r2, "ncclGroupEnd");
+  return 0;
+}
+
+// ---- the update -------------------------------------------------------------
+
+int dpk_zero_grads(dpk_handle* h, void* stream) {
+  if (!h) { set_error("dpk_zero_grads: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_zero_grads: buffers not bound"); return DPK_E_STATE; }
+  DPK_GUARD(h);
+  DPK_CUDA(cudaMemsetAsync(h->g, 0, (size_t)h->n_elems * elem_size(h->dtype), (cudaStream_t)stream));
+  return 0;
+}
+
+int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream) {
+  if (!h) { set_error("dpk_grad_norm: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_grad_norm: buffers not bound"); return DPK_E_STATE; }
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n_tiles = (int)h->tiles.size();
+  int rc = (h->dtype == DPK_F32) ? launch_sumsq<float>(h, 0, n_tiles, (float)inv_scale, st)
+                                 : launch_sumsq<__nv_bfloat16>(h, 0, n_tiles, (float)inv_scale, st);
+  if (rc) return rc;
+  if ((rc = launch_segment_reduce(h, h->d_partials_pre, st))) return rc;
+  if (h->dtype == DPK_F32)
+    finalize_norm_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->d_seg_bad, h->n_seg, (float)max_norm,
+                                                        h->d_seg_norms, h->d_results);
+  else
+    finalize_norm_kernel<__nv_bfloat16><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->d_seg_bad, h->n_seg,
+                                                                (float)max_norm, h->d_seg_norms, h->d_results);
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step, double inv_scale,
+                     int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode, void* stream) {
+  if (!h) { set_error("dpk_fused_update: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_fused_update: buffers not bound"); return DPK_E_STATE; }
+  if (adam_step < 1) { set_error("dpk_fused_update: adam_step %lld < 1", (long long)adam_step); return DPK_E_BADARG; }
+  if (grad_mode < DPK_GRAD_KEEP || grad_mode > DPK_GRAD_ZERO) { set_error("dpk_fused_update: bad grad_mode"); return DPK_E_BADARG; }
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+
+  // Python-double arithmetic of torch's _multi_tensor_adam (optim/adam.py:770-781),
+  // each value then narrowed to fp32 as a kernel argument.
+  StepScalars sc;
+  memset(&sc, 0, sizeof(sc));
+  const double step = (double)adam_step;
+  const double bc1 = 1.0 - pow(h->beta1, step);
+  const double bc2 = 1.0 - pow(h->beta2, step);
+  sc.inv_scale = (float)inv_scale;
+  sc.decay = (float)(1.0 - lr * weight_decay);
+  sc.has_decay = weight_decay != 0.0;
+  sc.w1 = (float)(1.0 - h->beta1);
+  sc.beta2 = (float)h->beta2;
+  sc.omb2 = (float)(1.0 - h->beta2);
+  sc.bc2_sqrt = (float)pow(bc2, 0.5);
+  sc.eps = (float)h->eps;
+  sc.neg_step = (float)((lr / bc1) * -1.0);
+  for (int k = 0; k < h->n_ema; ++k) {
+    sc.rate[k] = (float)h->ema_rates[k];
+    sc.alpha[k] = (float)(1.0 - h->ema_rates[k]);
+  }
+  int rc = (h->dtype == DPK_F32)
+               ? launch_update<float>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, st)
+               : launch_update<__nv_bfloat16>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, st);
+  if (rc) return rc;
+  if ((rc = launch_segment_reduce(h, h->d_partials_post, st))) return rc;
+  if (h->dtype == DPK_F32)
+    finalize_logged_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, skip_if_nonfinite, h->d_results);
+  else
+    finalize_logged_kernel<__nv_bfloat16><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, skip_if_nonfinite,
+                                                                 h->d_results);
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpk_result_ptr(dpk_handle* h, void** d_out) {
+  if (!h || !d_out) { set_error("dpk_result_ptr: null argument"); return DPK_E_BADARG; }
+  *d_out = h->d_results;
+  return 0;
+}
+
+int dpk_read_result_sync(dpk_handle* h, double* out, void* stream) {
+  if (!h || !out) { set_error("dpk_read_result_sync: null argument"); return DPK_E_BADARG; }
+  DPK_GUARD(h);
+  DPK_CUDA(cudaMemcpyAsync(h->h_results_pinned, h->d_results, DPK_R_COUNT * sizeof(double), cudaMemcpyDeviceToHost,
+                           (cudaStream_t)stream));
+  DPK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  memcpy(out, h->h_results_pinned, DPK_R_COUNT * sizeof(double));
+  return 0;
+}
+
+int dpk_segment_norms_ptr(dpk_handle* h, void** d_out) {
+  if (!h || !d_out) { set_error("dpk_segment_norms_ptr: null argument"); return DPK_E_BADARG; }
+  *d_out = h->d_seg_norms;
+  return 0;
+}
+
+int dpk_timing_enable(dpk_handle* h, int32_t on) {
+  if (!h) { set_error("dpk_timing_enable: null handle"); return DPK_E_BADARG; }
+  h->timing = on != 0;
+  return 0;
+}
+
+int dpk_timing_read_sync(dpk_handle* h, int32_t which, float* ms_out, int32_t cap, int32_t* n_out) {
+  if (!h || which < 0 || which > 1 || !n_out || (cap > 0 && !ms_out)) {
+    set_error("dpk_timing_read_sync: bad argument");
+    return DPK_E_BADARG;
+  }
+  DPK_GUARD(h);
+  int n = 0;
+  for (int i = 0; i < h->tcount[which]; ++i) {
+    cudaEvent_t b = h->tev[which][2 * i], e = h->tev[which][2 * i + 1];
+    DPK_CUDA(cudaEventSynchronize(e));
+    float ms = 0.f;
+    DPK_CUDA(cudaEventElapsedTime(&ms, b, e));
+    if (n < cap) ms_out[n++] = ms;
+  }
+  h->tcount[which] = 0;
+  *n_out = n;
+  return 0;
+}
+
+int dpk_launch_count(const dpk_handle* h, int64_t* out) {
+  if (!h || !out) { set_error("dpk_launch_count: null argument"); return DPK_E_BADARG; }
+  *out = h->launches;
+  return 0;
+}
+
+int dpk_ema_update(void* d_target, const void* d_source, int64_t n, int32_t dtype, double rate, void* stream) {
+  if (n < 0 || (dtype != DPK_F32 && dtype != DPK_BF16)) { set_error("dpk_ema_update: bad argument"); return DPK_E_BADARG; }
+  if (n == 0) return 0;
+  if (!d_target || !d_source) { set_error("dpk_ema_update: null pointer"); return DPK_E_BADARG; }
+  const int es = elem_size(dtype);
+  if (((uintptr_t)d_target % es) || ((uintptr_t)d_source % es)) { set_error("dpk_ema_update: pointer not element-aligned"); return DPK_E_BADARG; }
+  // leading scalars until both pointers are 16-byte aligned (possible only if
+  // they are congruent modulo 16)
+  long long head = n;
+  if ((((uintptr_t)d_target ^ (uintptr_t)d_source) & 15u) == 0) {
+    head = (long long)(((16 - ((uintptr_t)d_target & 15u)) & 15u) / es);
+    if (head > n) head = n;
+  }
+  const float ratef = (float)rate, alphaf = (float)(1.0 - rate);
+  int dev = 0, sm = 148;
+  DPK_CUDA(cudaGetDevice(&dev));
+  DPK_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+  const long long work = (n + (16 / es) - 1) / (16 / es);
+  const int grid = (int)std::max<long long>(1, std::min<long long>((work + kThreads - 1) / kThreads, 8LL * sm));
+  if (dtype == DPK_F32)
+    ema_update_kernel<float><<<grid, kThreads, 0, (cudaStream_t)stream>>>((float*)d_target, (const float*)d_source, n,
+                                                                         head, ratef, alphaf);
+  else
+    ema_update_kernel<__nv_bfloat16><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        (__nv_bfloat16*)d_target, (const __nv_bfloat16*)d_source, n, head, ratef, alphaf);
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,104 @@
+// Host-side internals shared by the translation units of libdpk.
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>  // types and enums only; the functions are bound with dlsym
+#include <stdint.h>
+#include <mutex>
+#include <string>
+#include <vector>
+#include "../../include/dpk.h"
+#include "dpk_kernels.cuh"
+
+namespace dpk {
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define DPK_CUDA(call)                                        \
+  do {                                                        \
+    cudaError_t e__ = (call);                                 \
+    if (e__ != cudaSuccess) return ::dpk::cuda_fail(e__, #call); \
+  } while (0)
+
+// NCCL is resolved at run time from the copy torch already loaded
+// (libnccl.so.2), so the library itself has no link-time NCCL dependency and
+// loads on machines without it.
+struct NcclApi {
+  bool ok = false;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*CommGetAsyncError)(ncclComm_t, ncclResult_t*) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+const NcclApi* nccl_api();  // nullptr (with dpk_last_error set) if unavailable
+int nccl_fail(ncclResult_t r, const char* what);
+
+#define DPK_NCCL(call)                                               \
+  do {                                                               \
+    ncclResult_t r__ = (call);                                       \
+    if (r__ != ncclSuccess) return ::dpk::nccl_fail(r__, #call);     \
+  } while (0)
+
+struct Bucket {
+  int seg_begin, seg_end;     // tensors [seg_begin, seg_end)
+  long long start, count;     // flat elements
+  int tile_begin, tile_end;   // tiles covering those tensors
+};
+
+}  // namespace dpk
+
+struct dpk_handle {
+  int dtype = DPK_F32;
+  int device = 0;
+  int n_seg = 0;
+  int n_ema = 0;
+  int tile_elems = 0;
+  long long n_elems = 0;
+  double beta1 = 0.9, beta2 = 0.999, eps = 1e-8;
+  double ema_rates[DPK_MAX_EMA] = {0};
+  std::vector<long long> seg_off, seg_len;
+  std::vector<dpk::Tile> tiles;          // host copy
+  std::vector<int> seg_tile_begin;       // [n_seg + 1]
+  std::vector<dpk::Bucket> buckets;
+  int sm_count = 148;
+
+  // borrowed
+  void* p = nullptr; void* g = nullptr; void* m = nullptr; void* v = nullptr;
+  void* ema[DPK_MAX_EMA] = {nullptr};
+  bool bound = false;
+
+  // owned device scratch
+  dpk::Tile* d_tiles = nullptr;
+  int* d_seg_tile_begin = nullptr;
+  dpk::TilePartial* d_partials_pre = nullptr;   // pass 1
+  dpk::TilePartial* d_partials_post = nullptr;  // pass 2
+  double* d_seg_sumsq = nullptr;
+  unsigned* d_seg_bad = nullptr;
+  double* d_seg_norms = nullptr;
+  double* d_results = nullptr;
+  double* h_results_pinned = nullptr;
+
+  // communication
+  ncclComm_t comm = nullptr;
+  int world = 1, rank = 0;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
+  bool any_enqueued = false;
+  std::mutex mu;
+
+  // instrumentation
+  bool timing = false;
+  std::vector<cudaEvent_t> tev[2];  // [which] -> begin,end,begin,end,...
+  int tcount[2] = {0, 0};
+  long long launches = 0;
+};

@@ -1,0 +1,464 @@
+// Device kernels of libdpk (sm_100a).  Everything here is HBM-bound streaming
+// work: 128-bit coalesced accesses, no data reuse, no tensor cores.
+//
+// Work decomposition: the flat buffers are cut on the host into *tiles* that
+// never straddle a parameter tensor (dpk.cu: build_tiles).  Both passes walk
+// the same tile table, so each tile yields one partial sum of squares that
+// belongs to exactly one tensor -- the per-tensor norms torch's
+// clip_grad_norm_ is defined over (nn/utils/clip_grad.py:92-108) fall out of a
+// deterministic second-level reduction, with no float atomics anywhere.
+//
+// Arithmetic mirrors the op sequence torch's CUDA foreach AdamW runs
+// (optim/adam.py:683-800) including where it rounds: every `__f*_rn` below is
+// one torch kernel's store.  The file is compiled with -fmad=false; the FMAs
+// torch's kernels get from nvcc's contraction are written out explicitly.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include "../../include/dpk.h"
+
+namespace dpk {
+
+constexpr int kThreads = 256;
+
+struct Tile {
+  long long start;  // element offset in the flat buffers (multiple of 16 bytes)
+  int len;          // elements in this tile (<= tile_elems)
+  int seg;          // parameter tensor it belongs to
+};
+
+struct TilePartial {
+  float sumsq;
+  unsigned bad;  // 1 if a non-finite gradient element was seen
+};
+
+// Host-computed scalars of one AdamW step, each already rounded to fp32 the
+// way torch rounds a Python double handed to a CUDA kernel.
+struct StepScalars {
+  float inv_scale;   // 1/2^lg_loss_scale, 1 when unused
+  float decay;       // 1 - lr*wd
+  int has_decay;     // torch skips the multiply when wd == 0
+  float w1;          // 1 - beta1
+  float beta2;
+  float omb2;        // 1 - beta2
+  float bc2_sqrt;    // sqrt(1 - beta2^t)
+  float eps;
+  float neg_step;    // -(lr / (1 - beta1^t))
+  float rate[DPK_MAX_EMA];
+  float alpha[DPK_MAX_EMA];  // fp32(1 - rate)
+};
+
+// ---------------------------------------------------------------- helpers --
+
+template <typename T> struct ElemTraits;
+template <> struct ElemTraits<float> {
+  static constexpr int VE = 4;  // elements per 16-byte vector
+  static __device__ __forceinline__ void unpack(const uint4& r, float* x) {
+    x[0] = __uint_as_float(r.x); x[1] = __uint_as_float(r.y);
+    x[2] = __uint_as_float(r.z); x[3] = __uint_as_float(r.w);
+  }
+  static __device__ __forceinline__ uint4 pack(const float* x) {
+    return make_uint4(__float_as_uint(x[0]), __float_as_uint(x[1]),
+                      __float_as_uint(x[2]), __float_as_uint(x[3]));
+  }
+  // value as stored in the state dtype
+  static __device__ __forceinline__ float rnd(float x) { return x; }
+};
+template <> struct ElemTraits<__nv_bfloat16> {
+  static constexpr int VE = 8;
+  static __device__ __forceinline__ void unpack(const uint4& r, float* x) {
+    const unsigned w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      x[2 * i] = __uint_as_float(w[i] << 16);
+      x[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  static __device__ __forceinline__ uint4 pack(const float* x) {
+    unsigned w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      // inputs are already bf16-representable: truncation is exact
+      w[i] = (__float_as_uint(x[2 * i]) >> 16) | (__float_as_uint(x[2 * i + 1]) & 0xffff0000u);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  static __device__ __forceinline__ float rnd(float x) {
+    return __bfloat162float(__float2bfloat16_rn(x));
+  }
+};
+
+// streaming 128-bit accesses: every byte is touched once per pass
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) { return __ldcs(p); }
+__device__ __forceinline__ uint4 ld_readonly(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream(uint4* p, const uint4& v) { __stcs(p, v); }
+
+__device__ __forceinline__ bool nonfinite_bits(float x) {
+  return (__float_as_uint(x) & 0x7f800000u) == 0x7f800000u;
+}
+
+// Block-wide sum in a fixed order (lane tree, then warp 0 over the warp
+// totals): same inputs -> same bits, run to run.
+__device__ __forceinline__ float block_sum(float v, float* smem /*[kThreads/32]*/) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = __fadd_rn(v, __shfl_down_sync(0xffffffffu, v, o));
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (warp == 0) {
+    r = (lane < kThreads / 32) ? smem[lane] : 0.f;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) r = __fadd_rn(r, __shfl_down_sync(0xffffffffu, r, o));
+  }
+  __syncthreads();
+  return r;  // valid in thread 0
+}
+
+__device__ __forceinline__ double block_sum_f64(double v, double* smem) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) smem[warp] = v;
+  __syncthreads();
+  double r = 0.0;
+  if (warp == 0) {
+    r = (lane < kThreads / 32) ? smem[lane] : 0.0;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) r += __shfl_down_sync(0xffffffffu, r, o);
+  }
+  __syncthreads();
+  return r;
+}
+
+// ------------------------------------------------------- pass 1: sum sq ----
+// Reads g once (s bytes/param).  One partial per tile.
+
+template <typename T, int U>
+__global__ void __launch_bounds__(kThreads)
+sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin,
+                   int tile_end, float inv_scale, TilePartial* __restrict__ partials) {
+  using Tr = ElemTraits<T>;
+  constexpr int VE = Tr::VE;
+  __shared__ float red[kThreads / 32];
+  for (int t = tile_begin + blockIdx.x; t < tile_end; t += gridDim.x) {
+    const Tile tile = tiles[t];
+    const uint4* gv = reinterpret_cast<const uint4*>(g + tile.start);
+    const int nvec = (tile.len + VE - 1) / VE;
+    float acc = 0.f;
+    unsigned bad = 0;
+    for (int v0 = threadIdx.x; v0 < nvec; v0 += kThreads * U) {
+      uint4 raw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * kThreads;
+        raw[u] = (v < nvec) ? ld_readonly(gv + v) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * kThreads;
+        float x[VE];
+        Tr::unpack(raw[u], x);
+        const int rem = tile.len - v * VE;  // valid lanes in this vector (<=0: none)
+#pragma unroll
+        for (int j = 0; j < VE; ++j) {
+          if (j < rem) {
+            const float y = Tr::rnd(__fmul_rn(x[j], inv_scale));
+            bad |= nonfinite_bits(y) ? 1u : 0u;
+            acc = __fmaf_rn(y, y, acc);
+          }
+        }
+      }
+    }
+    const int any_bad = __syncthreads_or((int)bad);
+    const float s = block_sum(acc, red);
+    if (threadIdx.x == 0) {
+      TilePartial p;
+      p.sumsq = s;
+      p.bad = any_bad ? 1u : 0u;
+      partials[t] = p;
+    }
+  }
+}
+
+// Second level: one block per tensor sums that tensor's tile partials in fp64.
+static __global__ void __launch_bounds__(kThreads)
+segment_reduce_kernel(const TilePartial* __restrict__ partials,
+                      const int* __restrict__ seg_tile_begin /*[n_seg+1]*/,
+                      double* __restrict__ seg_sumsq, unsigned* __restrict__ seg_bad, int n_seg) {
+  __shared__ double red[kThreads / 32];
+  for (int s = blockIdx.x; s < n_seg; s += gridDim.x) {
+    const int b = seg_tile_begin[s], e = seg_tile_begin[s + 1];
+    double acc = 0.0;
+    unsigned bad = 0;
+    for (int t = b + threadIdx.x; t < e; t += kThreads) {
+      const TilePartial p = partials[t];
+      acc += (double)p.sumsq;
+      bad |= p.bad;
+    }
+    const int any_bad = __syncthreads_or((int)bad);
+    const double tot = block_sum_f64(acc, red);
+    if (threadIdx.x == 0) {
+      seg_sumsq[s] = tot;
+      seg_bad[s] = any_bad ? 1u : 0u;
+    }
+  }
+}
+
+// Third level (one block): per-tensor norms -> total norm -> clip coefficient,
+// rounding where torch rounds (clip_grad.py:96-108 and :165-169; for bf16 each
+// intermediate is a bf16 tensor).
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+finalize_norm_kernel(const double* __restrict__ seg_sumsq, const unsigned* __restrict__ seg_bad,
+                     int n_seg, float max_norm, double* __restrict__ seg_norms,
+                     double* __restrict__ results) {
+  using Tr = ElemTraits<T>;
+  __shared__ double red[kThreads / 32];
+  double acc = 0.0;
+  unsigned bad = 0;
+  for (int s = threadIdx.x; s < n_seg; s += kThreads) {
+    const float n = Tr::rnd(__fsqrt_rn((float)seg_sumsq[s]));  // _foreach_norm output
+    seg_norms[s] = (double)n;
+    acc += (double)n * (double)n;
+    bad |= seg_bad[s];
+  }
+  const int any_bad = __syncthreads_or((int)bad);
+  const double tot2 = block_sum_f64(acc, red);
+  if (threadIdx.x == 0) {
+    const float total = Tr::rnd(__fsqrt_rn((float)tot2));  // vector_norm(stack(norms))
+    float coef = 1.f;
+    if (max_norm > 0.f) {
+      // max_norm / (total + 1e-6) is Tensor.__rdiv__: reciprocal() * max_norm
+      const float denom = Tr::rnd(__fadd_rn(total, 1e-6f));
+      const float rcp = Tr::rnd(__fdiv_rn(1.0f, denom));
+      coef = Tr::rnd(__fmul_rn(rcp, max_norm));
+      coef = (coef > 1.0f) ? 1.0f : coef;  // clamp(max=1); NaN stays NaN
+    }
+    results[DPK_R_TOTAL_NORM] = (double)total;
+    results[DPK_R_CLIP_COEF] = (double)coef;
+    results[DPK_R_NONFINITE] = any_bad ? 1.0 : 0.0;
+  }
+}
+
+// After the fused pass: what TrainLoop._log_grad_norm computes on the grads the
+// step used -- sqrt(sum_i float64((g_i**2).sum())) (utils/trainer.py:265-271).
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+finalize_logged_kernel(const double* __restrict__ seg_sumsq, int n_seg, int skip_if_nonfinite,
+                       double* __restrict__ results) {
+  using Tr = ElemTraits<T>;
+  __shared__ double red[kThreads / 32];
+  const bool skipped = skip_if_nonfinite && results[DPK_R_NONFINITE] != 0.0;
+  double acc = 0.0;
+  if (!skipped)
+    for (int s = threadIdx.x; s < n_seg; s += kThreads)
+      acc += (double)Tr::rnd((float)seg_sumsq[s]);  // .sum() returns the grad dtype
+  const double tot = block_sum_f64(acc, red);
+  if (threadIdx.x == 0) {
+    if (!skipped) results[DPK_R_LOGGED_NORM] = sqrt(tot);
+    results[DPK_R_SKIPPED] = skipped ? 1.0 : 0.0;
+  }
+}
+
+// ------------------------------------------------ pass 2: the fused update --
+// Reads g,p,m,v and K EMA copies, writes p,m,v and K EMA copies: (7+2K)*s
+// bytes per parameter (+s if the gradient is rewritten or zeroed).
+
+template <typename T, int K>
+struct UpdateArgs {
+  T* p;
+  T* g;
+  T* m;
+  T* v;
+  T* ema[K > 0 ? K : 1];
+  const Tile* tiles;
+  int n_tiles;
+  TilePartial* partials;   // post-scale sum of squares per tile
+  const double* results;   // result block of the norm pass
+  int use_clip_coef;
+  int skip_if_nonfinite;
+  StepScalars s;
+};
+
+template <typename T, int K, int GM, bool FULL>
+__device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long long vidx, int rem,
+                                              float coef, float& acc) {
+  using Tr = ElemTraits<T>;
+  constexpr int VE = Tr::VE;
+  uint4* pv = reinterpret_cast<uint4*>(a.p) + vidx;
+  uint4* gv = reinterpret_cast<uint4*>(a.g) + vidx;
+  uint4* mv = reinterpret_cast<uint4*>(a.m) + vidx;
+  uint4* vv = reinterpret_cast<uint4*>(a.v) + vidx;
+
+  const uint4 rg = (GM == DPK_GRAD_KEEP) ? ld_readonly(gv) : ld_stream(gv);
+  const uint4 rp = ld_stream(pv);
+  const uint4 rm = ld_stream(mv);
+  const uint4 rv = ld_stream(vv);
+  uint4 re[K > 0 ? K : 1];
+#pragma unroll
+  for (int k = 0; k < K; ++k) re[k] = ld_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx);
+
+  float g[VE], p[VE], m[VE], v[VE];
+  Tr::unpack(rg, g);
+  Tr::unpack(rp, p);
+  Tr::unpack(rm, m);
+  Tr::unpack(rv, v);
+  const StepScalars& s = a.s;
+
+#pragma unroll
+  for (int j = 0; j < VE; ++j) {
+    // grad.mul_(1/2^lg) (upstream loss-scale), then _foreach_mul_(grads, coef)
+    float gj = Tr::rnd(__fmul_rn(g[j], s.inv_scale));
+    gj = Tr::rnd(__fmul_rn(gj, coef));
+    // (p.grad ** 2).sum(): the square is a tensor of the grad dtype
+    const float sq = Tr::rnd(__fmul_rn(gj, gj));
+    if (FULL || j < rem) acc = __fadd_rn(acc, sq);
+    // _foreach_mul_(params, 1 - lr*wd), skipped when wd == 0
+    float pj = s.has_decay ? Tr::rnd(__fmul_rn(p[j], s.decay)) : p[j];
+    // _foreach_lerp_(exp_avg, grad, 1-beta1): m + w*(g-m), w < 0.5
+    const float mj = Tr::rnd(__fmaf_rn(s.w1, __fsub_rn(gj, m[j]), m[j]));
+    // _foreach_mul_(exp_avg_sq, beta2); _foreach_addcmul_(exp_avg_sq, g, g, 1-beta2)
+    float vj = Tr::rnd(__fmul_rn(v[j], s.beta2));
+    vj = Tr::rnd(__fmaf_rn(s.omb2, __fmul_rn(gj, gj), vj));
+    // _foreach_sqrt; _foreach_div_(bc2_sqrt); _foreach_add_(eps)
+    float d = Tr::rnd(__fsqrt_rn(vj));
+    d = Tr::rnd(__fdiv_rn(d, s.bc2_sqrt));
+    d = Tr::rnd(__fadd_rn(d, s.eps));
+    // _foreach_addcdiv_(params, exp_avg, denom, -step_size)
+    pj = Tr::rnd(__fmaf_rn(s.neg_step, __fdiv_rn(mj, d), pj));
+    g[j] = gj;
+    p[j] = pj;
+    m[j] = mj;
+    v[j] = vj;
+  }
+
+  if (FULL) {
+    st_stream(pv, Tr::pack(p));
+    st_stream(mv, Tr::pack(m));
+    st_stream(vv, Tr::pack(v));
+    if (GM == DPK_GRAD_CLIPPED) st_stream(gv, Tr::pack(g));
+    if (GM == DPK_GRAD_ZERO) st_stream(gv, make_uint4(0, 0, 0, 0));
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      float e[VE];
+      Tr::unpack(re[k], e);
+#pragma unroll
+      for (int j = 0; j < VE; ++j) {
+        // update_ema: trg.mul_(rate).add_(src, alpha=1-rate)  (utils/trainer.py:370)
+        const float t = Tr::rnd(__fmul_rn(e[j], s.rate[k]));
+        e[j] = Tr::rnd(__fmaf_rn(s.alpha[k], p[j], t));
+      }
+      st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, Tr::pack(e));
+    }
+  } else {
+    // ragged last vector of a tensor: lanes past the end keep their bytes
+    float op[VE], om[VE], ov[VE], og[VE];
+    Tr::unpack(rp, op);
+    Tr::unpack(rm, om);
+    Tr::unpack(rv, ov);
+    Tr::unpack(rg, og);
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      if (j >= rem) { p[j] = op[j]; m[j] = om[j]; v[j] = ov[j]; g[j] = og[j]; }
+      else if (GM == DPK_GRAD_ZERO) g[j] = 0.f;
+    }
+    st_stream(pv, Tr::pack(p));
+    st_stream(mv, Tr::pack(m));
+    st_stream(vv, Tr::pack(v));
+    if (GM != DPK_GRAD_KEEP) st_stream(gv, Tr::pack(g));
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      float e[VE];
+      Tr::unpack(re[k], e);
+#pragma unroll
+      for (int j = 0; j < VE; ++j) {
+        if (j < rem) {
+          const float t = Tr::rnd(__fmul_rn(e[j], s.rate[k]));
+          e[j] = Tr::rnd(__fmaf_rn(s.alpha[k], p[j], t));
+        }
+      }
+      st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, Tr::pack(e));
+    }
+  }
+}
+
+template <typename T, int K, int GM, int U>
+__global__ void __launch_bounds__(kThreads)
+fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
+  using Tr = ElemTraits<T>;
+  constexpr int VE = Tr::VE;
+  __shared__ float red[kThreads / 32];
+  if (a.skip_if_nonfinite && a.results[DPK_R_NONFINITE] != 0.0) return;
+  const float coef = a.use_clip_coef ? (float)a.results[DPK_R_CLIP_COEF] : 1.0f;
+
+  for (int t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+    const Tile tile = a.tiles[t];
+    const long long vbase = tile.start / VE;
+    const int nfull = tile.len / VE;  // vectors with every lane valid
+    const int nvec = (tile.len + VE - 1) / VE;
+    float acc = 0.f;
+    for (int v0 = threadIdx.x; v0 < nfull; v0 += kThreads * U) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * kThreads;
+        if (v < nfull) update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
+      }
+    }
+    if (nvec != nfull && threadIdx.x == 0)
+      update_vector<T, K, GM, false>(a, vbase + nfull, tile.len - nfull * VE, coef, acc);
+    const float s = block_sum(acc, red);
+    if (threadIdx.x == 0) {
+      TilePartial p;
+      p.sumsq = s;
+      p.bad = 0;
+      a.partials[t] = p;
+    }
+  }
+}
+
+// ------------------------------------------------------ stand-alone EMA ----
+// update_ema(target, source, rate) on arbitrary contiguous arrays.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+ema_update_kernel(T* __restrict__ trg, const T* __restrict__ src, long long n, long long head,
+                  float rate, float alpha) {
+  using Tr = ElemTraits<T>;
+  constexpr int VE = Tr::VE;
+  auto one = [&](long long i) {
+    float e, s;
+    if constexpr (sizeof(T) == 4) { e = trg[i]; s = src[i]; }
+    else { e = __bfloat162float(trg[i]); s = __bfloat162float(src[i]); }
+    const float t = Tr::rnd(__fmul_rn(e, rate));
+    const float r = Tr::rnd(__fmaf_rn(alpha, s, t));
+    if constexpr (sizeof(T) == 4) trg[i] = r; else trg[i] = __float2bfloat16_rn(r);
+  };
+  const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+  const long long nthreads = (long long)gridDim.x * kThreads;
+  // `head` leading elements bring both pointers to 16-byte alignment
+  // (head == n when they cannot be co-aligned: all-scalar path)
+  for (long long i = tid; i < head; i += nthreads) one(i);
+  const long long nvec = (n - head) / VE;
+  uint4* tv = reinterpret_cast<uint4*>(trg + head);
+  const uint4* sv = reinterpret_cast<const uint4*>(src + head);
+  for (long long v = tid; v < nvec; v += nthreads) {
+    float e[VE], s[VE];
+    Tr::unpack(ld_stream(tv + v), e);
+    Tr::unpack(ld_readonly(sv + v), s);
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      const float t = Tr::rnd(__fmul_rn(e[j], rate));
+      e[j] = Tr::rnd(__fmaf_rn(alpha, s[j], t));
+    }
+    st_stream(tv + v, Tr::pack(e));
+  }
+  for (long long i = head + nvec * VE + tid; i < n; i += nthreads) one(i);
+}
+
+}  // namespace dpk

@@ -1,0 +1,124 @@
+"""``FusedAdamW``: the object ``TrainLoop.opt`` holds.
+
+It stands where ``torch.optim.AdamW(master_params, lr, weight_decay)`` stands in
+the reference (``utils/trainer.py:99``) and offers the parts of the optimizer
+surface the reference touches: ``param_groups[i]["lr"]`` (``:262-263``),
+``step()`` (``:242``), ``state_dict()/load_state_dict()`` in torch's own layout
+(``:173``, ``:302``) and the optional ``clip_grad_norm`` hook ``grad_clip``
+looks for (``:248-250``).  ``step()`` is one kernel launch: unscale, clip,
+AdamW and every EMA rate.
+"""
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from .engine import Engine
+from .flat import FlatState
+
+
+class FusedAdamW:
+    def __init__(self, params: Sequence[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999),
+                 eps: float = 1e-8, weight_decay: float = 1e-2, ema_rates: Sequence[float] = (),
+                 bucket_cap_mb: float = 128, grad_mode: int = _lib.GRAD_CLIPPED, tile_elems: int = 0):
+        params = list(params)
+        self.flat = FlatState(params, n_ema=len(ema_rates))
+        self.engine = Engine(self.flat.layout, self.flat.dtype, self.flat.device, ema_rates, betas, eps,
+                             bucket_cap_bytes=int(bucket_cap_mb * 1024 * 1024), tile_elems=tile_elems)
+        f = self.flat
+        self.engine.bind(f.params, f.grads, f.exp_avg, f.exp_avg_sq, f.emas)
+        self.defaults = dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay, amsgrad=False,
+                             maximize=False, foreach=None, capturable=False, differentiable=False, fused=None,
+                             decoupled_weight_decay=True)
+        self.param_groups: List[Dict] = [dict(self.defaults, params=params)]
+        self.ema_rates = [float(r) for r in ema_rates]
+        self.grad_mode = grad_mode
+        self.step_count = 0          # AdamW's per-parameter `step`, identical for all
+        self.inv_scale = 1.0         # 1/2^lg_loss_scale for the next step
+        self.skip_if_nonfinite = False
+        self._clip_pending = False
+        # one flag per EMA rate: set by step(), consumed by trainer.update_ema
+        self.ema_done = [False] * len(self.ema_rates)
+
+    # ---- what TrainLoop calls ----------------------------------------------
+    def clip_grad_norm(self, max_norm: float):
+        """Pass 1.  The coefficient stays on the device; step() applies it."""
+        self.engine.grad_norm(self.inv_scale, float(max_norm))
+        self._clip_pending = True
+
+    def check_finite(self):
+        """Pass 1 without clipping: fills the non-finite flag for a loss-scaled step."""
+        self.engine.grad_norm(self.inv_scale, 0.0)
+        self._clip_pending = False
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        if closure is not None:
+            raise NotImplementedError("FusedAdamW.step does not take a closure")
+        g = self.param_groups[0]
+        b1, b2 = g["betas"]
+        if (b1, b2) != self.engine.betas or g["eps"] != self.engine.eps:
+            raise ValueError("betas/eps are fixed when the optimizer is created")
+        self.step_count += 1
+        self.engine.fused_update(float(g["lr"]), float(g["weight_decay"]), self.step_count,
+                                 inv_scale=self.inv_scale, use_clip_coef=self._clip_pending,
+                                 skip_if_nonfinite=self.skip_if_nonfinite, grad_mode=self.grad_mode)
+        self._clip_pending = False
+        self.ema_done = [True] * len(self.ema_rates)
+
+    def undo_step_count(self):
+        """A predicated-off (non-finite) step must not advance AdamW's step."""
+        self.step_count -= 1
+        self.ema_done = [False] * len(self.ema_rates)
+
+    def zero_grad(self, set_to_none: bool = False):
+        if set_to_none:
+            raise ValueError("gradients are views of the flat buffer and cannot be set to None")
+        self.engine.zero_grads()
+
+    # ---- torch.optim.AdamW-compatible checkpoint layout -----------------------
+    @property
+    def state(self) -> Dict[torch.nn.Parameter, Dict[str, torch.Tensor]]:
+        if self.step_count == 0:
+            return {}
+        f = self.flat
+        return {p: {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
+                for p, m, v in zip(f.param_list, f.exp_avg_views, f.exp_avg_sq_views)}
+
+    def state_dict(self) -> Dict:
+        f = self.flat
+        state = {}
+        if self.step_count:
+            for i, (m, v) in enumerate(zip(f.exp_avg_views, f.exp_avg_sq_views)):
+                state[i] = {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
+        groups = []
+        for g in self.param_groups:
+            d = {k: v for k, v in g.items() if k != "params"}
+            d["params"] = list(range(len(g["params"])))
+            groups.append(d)
+        return {"state": state, "param_groups": groups}
+
+    @torch.no_grad()
+    def load_state_dict(self, sd: Dict):
+        f = self.flat
+        groups = sd["param_groups"]
+        if len(groups) != 1 or len(groups[0]["params"]) != len(f.param_list):
+            raise ValueError("loaded state dict has a different parameter-group layout")
+        for k, v in groups[0].items():
+            if k != "params":
+                self.param_groups[0][k] = v
+        state = sd["state"]
+        if not state:
+            self.step_count = 0
+            f.exp_avg.zero_()
+            f.exp_avg_sq.zero_()
+            return
+        steps = set()
+        for i, (m, v) in enumerate(zip(f.exp_avg_views, f.exp_avg_sq_views)):
+            st = state[i] if i in state else state[str(i)]
+            m.copy_(st["exp_avg"])
+            v.copy_(st["exp_avg_sq"])
+            steps.add(int(float(st["step"])))
+        if len(steps) != 1:
+            raise ValueError("parameters with different AdamW step counts cannot share one fused step")
+        self.step_count = steps.pop()

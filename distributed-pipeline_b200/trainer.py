@@ -1,0 +1,461 @@
+"""Drop-in ``TrainLoop`` whose post-backward update runs on libdpk.
+
+Method surface, constructor keywords, attributes and checkpoint file names are
+those of the reference's ``utils/trainer.py`` (cited per method) so that
+``run/train.py:103-121`` and user subclasses work unchanged.  What is different
+is what happens underneath ``forward_backward()`` and ``optimize()``:
+
+===========================  ==================================================
+reference                    here
+===========================  ==================================================
+209 ``grad.zero_()``         one fill of the flat gradient buffer
+torch DDP reducer            in-place ``ncclAllReduce`` per flat bucket, launched
+                             from grad hooks on a side stream
+``clip_grad_norm_``          pass 1 kernel, coefficient stays on the device
+209 ``.item()`` syncs        one asynchronous 64-byte read-back per step
+foreach AdamW + 2K EMA ops   one fused kernel (pass 2)
+===========================  ==================================================
+
+There is no CPU path: constructing a ``TrainLoop`` around a model that is not
+on a CUDA device raises.
+"""
+import math
+import os
+import weakref
+from typing import Dict, List, Optional
+
+import torch
+
+from . import _lib, dist_util
+from . import logger as _default_logger
+from .engine import ema_update as _ema_update_kernel
+from .optim import FusedAdamW
+from .reducer import BucketReducer, FlatDDP
+
+INITIAL_LOG_LOSS_SCALE = 20.0  # upstream fp16 path (absent from the reference)
+
+_GRAD_MODES = {"keep": _lib.GRAD_KEEP, "clipped": _lib.GRAD_CLIPPED, "zero": _lib.GRAD_ZERO}
+
+# id(list of EMA tensors) -> (weakref to FusedAdamW, rate index); lets the
+# module-level update_ema recognise lists the fused step already advanced.
+_FUSED_EMA_LISTS: Dict[int, tuple] = {}
+
+
+class TrainLoop:
+
+    # ---- user hooks (reference utils/trainer.py:19-43) ------------------------
+    def log_loss_dict(self, mode, losses, *args, **kwargs):
+        raise NotImplementedError
+
+    def compute_losses(self, micro_batch):
+        raise NotImplementedError
+
+    @staticmethod
+    def backward_from_losses(losses):
+        raise NotImplementedError("override backward_from_losses: reduce `losses` to a scalar and call .backward()")
+
+    @classmethod
+    def get_batch_length(cls, batch):
+        if isinstance(batch, torch.Tensor):
+            return batch.shape[0]
+        if isinstance(batch, dict):
+            return cls.get_batch_length(next(iter(batch.values())))
+        if isinstance(batch, list):
+            return cls.get_batch_length(batch[0])
+        raise TypeError("Unsupported batch type: {}".format(type(batch).__name__))
+
+    # ---- construction (reference :45-132) -------------------------------------
+    def __init__(
+            self,
+            *,
+            model,
+            data,
+            batch_size,
+            microbatch,
+            lr,
+            ema_rate,
+            log_interval,
+            save_interval,
+            resume_checkpoint,
+            weight_decay=0.0,
+            learning_steps=0,
+            checkpoint_path='',
+            gradient_clipping=-1.,
+            eval_data=None,
+            eval_interval=-1,
+            eval_callbacks=(),
+            # --- additions (all optional) ---
+            grads_after_step="clipped",   # "clipped" = what the reference leaves in .grad; "keep"; "zero"
+            use_fp16=False,               # upstream loss-scale state machine
+            fp16_scale_growth=1e-3,
+            logger=None,                  # module/object with logkv, logkv_mean, dumpkvs, log, get_current
+    ):
+        self.logger = logger if logger is not None else _default_logger
+        self.model = model
+        self.data = data
+        self.eval_data = eval_data
+        self.batch_size = batch_size
+        self.microbatch = microbatch if microbatch > 0 else batch_size
+        self.lr = float(lr)
+        self.ema_rate = [ema_rate] if isinstance(ema_rate, float) else [float(x) for x in ema_rate.split(",")]
+        self.log_interval = log_interval
+        self.eval_interval = eval_interval
+        self.save_interval = save_interval
+        self.resume_checkpoint = resume_checkpoint
+        self.weight_decay = weight_decay
+        self.learning_steps = learning_steps
+        self.gradient_clipping = gradient_clipping
+        self.use_fp16 = bool(use_fp16)
+        self.fp16_scale_growth = fp16_scale_growth
+        self.lg_loss_scale = INITIAL_LOG_LOSS_SCALE
+        if grads_after_step not in _GRAD_MODES:
+            raise ValueError(f"grads_after_step must be one of {sorted(_GRAD_MODES)}")
+
+        self.step = 0
+        self.resume_step = 0
+        self.global_batch = self.batch_size * dist_util.get_world_size()
+        self.eval_callbacks = list(eval_callbacks)
+        self.checkpoint_path = checkpoint_path
+
+        self.model_params = list(self.model.parameters())
+        self.master_params = self.model_params  # no fp32 master copy, as the reference (:91-92)
+        if not self.model_params or self.model_params[0].device.type != "cuda":
+            raise RuntimeError("TrainLoop needs the model on a CUDA device: the update path is CUDA-only "
+                               "(move it with model.to(dist_util.dev()) as run/train.py:75 does)")
+
+        self._load_and_sync_parameters()
+
+        # From here on parameters, gradients, moments and EMA copies are views
+        # of flat buffers; the lists above keep pointing at the same Parameters.
+        self.opt = FusedAdamW(self.master_params, lr=self.lr, weight_decay=self.weight_decay,
+                              ema_rates=self.ema_rate, bucket_cap_mb=128,
+                              grad_mode=_GRAD_MODES[grads_after_step])
+        self.ema_params = self.opt.flat.ema_views  # K lists of per-parameter tensors (:111-113)
+        for k, lst in enumerate(self.ema_params):
+            _FUSED_EMA_LISTS[id(lst)] = (weakref.ref(self.opt), k)
+        if self.resume_step:
+            self._load_optimizer_state()
+            for k, rate in enumerate(self.ema_rate):
+                self._load_ema_parameters(rate, k)
+
+        if dist_util.is_initialized():
+            self.use_ddp = True
+            # DDP's constructor broadcast (rank 0's parameters win), one coalesced
+            # collective; EMA copies follow the broadcast parameters on every rank
+            # (the reference leaves rank != 0 EMA copies at their local init, F4).
+            self.opt.engine.init_comm()
+            self.opt.engine.broadcast_state(root=0, include_ema=True)
+            self._reducer = BucketReducer(self.opt.flat, self.opt.engine)
+            self.ddp_model = FlatDDP(self.model, self._reducer)
+        else:
+            self.use_ddp = False
+            self._reducer = None
+            self.ddp_model = self.model
+
+        self._in_optimize = False
+        self._norm_requested = False
+        self._norm_inflight: List[tuple] = []
+        self._grads_are_zero = True  # fresh buffer
+        torch.cuda.empty_cache()
+
+    # ---- resume (reference :136-173) -----------------------------------------
+    def _load_and_sync_parameters(self):
+        resume_checkpoint = self.find_resume_checkpoint(self.logger) or self.resume_checkpoint
+        if not resume_checkpoint:
+            return
+        self.resume_step = self.parse_resume_step_from_filename(resume_checkpoint)
+        if dist_util.get_rank() == 0:
+            self.logger.log(f"loading model from checkpoint: {resume_checkpoint}...")
+            self.model.load_state_dict(dist_util.load_state_dict(resume_checkpoint, map_location=dist_util.dev()))
+        dist_util.sync_params(self.model.parameters())
+
+    def _load_ema_parameters(self, rate, k=None):
+        if k is None:
+            k = self.ema_rate.index(rate)
+        views = self.ema_params[k]
+        main_checkpoint = self.find_resume_checkpoint(self.logger) or self.resume_checkpoint
+        if not main_checkpoint:
+            return views
+        ema_checkpoint = self.find_ema_checkpoint(main_checkpoint, self.resume_step, rate)
+        if ema_checkpoint and dist_util.get_rank() == 0:
+            self.logger.log(f"loading EMA from checkpoint: {ema_checkpoint}...")
+            state_dict = dist_util.load_state_dict(ema_checkpoint, map_location=dist_util.dev())
+            with torch.no_grad():
+                for dst, src in zip(views, self._state_dict_to_master_params(state_dict)):
+                    dst.copy_(src)
+        dist_util.sync_params(views)
+        return views
+
+    def _load_optimizer_state(self):
+        main_checkpoint = self.find_resume_checkpoint(self.logger) or self.resume_checkpoint
+        if not main_checkpoint:
+            return
+        opt_checkpoint = self.find_opt_checkpoint(main_checkpoint, self.resume_step)
+        if opt_checkpoint and os.path.exists(opt_checkpoint):
+            self.logger.log(f"loading optimizer state from checkpoint: {opt_checkpoint}")
+            self.opt.load_state_dict(dist_util.load_state_dict(opt_checkpoint, map_location=dist_util.dev()))
+
+    # ---- the loop (reference :175-201) ---------------------------------------
+    def run_loop(self):
+        while not self.learning_steps or self.step + self.resume_step < self.learning_steps:
+            batch = next(self.data)
+            self.run_step(batch)
+            if self.step % self.log_interval == 0:
+                self.flush_logs()
+                self.logger.dumpkvs()
+            if self.eval_data is not None and self.step % self.eval_interval == 0:
+                self.forward_only(next(self.eval_data))
+                print('eval on validation set')
+                self.logger.dumpkvs()
+                if dist_util.get_rank() == 0:
+                    for callback in self.eval_callbacks:
+                        callback(self)
+            if self.step > 0 and self.step % self.save_interval == 0:
+                self.save()
+            self.step += 1
+        if (self.step - 1) % self.save_interval != 0:
+            self.save()
+
+    __call__ = run_loop
+
+    def run_step(self, batch):
+        self.forward_backward(batch)
+        self.optimize()
+        self.log_step()
+
+    def _zero_grad(self):
+        # reference :203-207 zeroes 209 tensors one by one; one fill here, and
+        # none at all when the fused pass already left the buffer zeroed.
+        if not self._grads_are_zero:
+            self.opt.engine.zero_grads()
+        self._grads_are_zero = True
+
+    def _common_forward(self, total_batch, start_index):
+        micro_batch = {
+            k: v[start_index: start_index + self.microbatch].to(dist_util.dev(), non_blocking=True)
+            for k, v in total_batch.items()
+        }
+        last_batch = (start_index + self.microbatch) >= self.get_batch_length(total_batch)
+        if last_batch or not self.use_ddp:
+            return self.compute_losses(micro_batch)
+        with self.ddp_model.no_sync():
+            return self.compute_losses(micro_batch)
+
+    @torch.no_grad()
+    def forward_only(self, batch):
+        self._zero_grad()
+        for i in range(0, self.get_batch_length(batch), self.microbatch):
+            losses = self._common_forward(batch, i)
+            self.log_loss_dict(mode="eval", losses=losses)
+
+    def forward_backward(self, batch):
+        self._zero_grad()
+        for i in range(0, self.get_batch_length(batch), self.microbatch):
+            losses = self._common_forward(batch, i)
+            self.log_loss_dict(mode="eval", losses=losses)  # sic: the reference logs "eval" here (:234)
+            if self.use_fp16:
+                scale = 2.0 ** self.lg_loss_scale
+                losses = {k: v * scale for k, v in losses.items()}
+            self._grads_are_zero = False
+            self.backward_from_losses(losses)
+
+    # ---- the update (reference :237-275) -------------------------------------
+    def optimize(self):
+        self._drain_norms(block=False)
+        if self.use_fp16:
+            return self._optimize_fp16()
+        self._in_optimize = True
+        try:
+            if self.gradient_clipping > 0:
+                self.grad_clip()
+            self._log_grad_norm()
+            self._anneal_lr()
+            self.opt.step()
+            for rate, params in zip(self.ema_rate, self.ema_params):
+                update_ema(params, self.master_params, rate=rate)
+        finally:
+            self._in_optimize = False
+        self._after_fused_step()
+
+    def _optimize_fp16(self):
+        """Upstream ``optimize_fp16``: skip the step and halve the scale when any
+        gradient is non-finite, else unscale, step, and grow the scale.  The test
+        and the skip both happen on the device; the host reads one flag."""
+        opt = self.opt
+        opt.inv_scale = 1.0 / (2.0 ** self.lg_loss_scale)
+        opt.skip_if_nonfinite = True
+        try:
+            if self.gradient_clipping > 0:
+                self.grad_clip()
+            else:
+                opt.check_finite()
+            self._anneal_lr()
+            opt.step()
+            res = opt.engine.read_results_sync()
+        finally:
+            opt.inv_scale = 1.0
+            opt.skip_if_nonfinite = False
+        if res[_lib.R_SKIPPED]:
+            opt.undo_step_count()
+            self.lg_loss_scale -= 1
+            self.logger.log(f"Found NaN, decreased lg_loss_scale to {self.lg_loss_scale}")
+            return
+        self.logger.logkv_mean("grad_norm", res[_lib.R_LOGGED_NORM])
+        for rate, params in zip(self.ema_rate, self.ema_params):
+            update_ema(params, self.master_params, rate=rate)
+        self.lg_loss_scale += self.fp16_scale_growth
+        if opt.grad_mode == _lib.GRAD_ZERO:
+            self._grads_are_zero = True
+
+    def grad_clip(self):
+        max_grad_norm = self.gradient_clipping
+        if hasattr(self.opt, "clip_grad_norm"):
+            # the reference's own seam for optimizers that clip themselves (:248-250)
+            self.opt.clip_grad_norm(max_grad_norm)
+        else:
+            torch.nn.utils.clip_grad_norm_(self.model.parameters(), max_grad_norm)
+
+    def _anneal_lr(self):
+        if not self.learning_steps:
+            return
+        frac_done = (self.step + self.resume_step) / self.learning_steps
+        lr = self.lr * (1 - frac_done)
+        for param_group in self.opt.param_groups:
+            param_group["lr"] = lr
+
+    def _log_grad_norm(self):
+        """Reference :265-271 reads 209 sums back one by one.  Inside optimize()
+        the value comes for free from the fused pass and is read back
+        asynchronously; called on its own it costs one norm pass and one read."""
+        if self._in_optimize:
+            self._norm_requested = True
+            return
+        self.opt.check_finite()
+        res = self.opt.engine.read_results_sync()
+        self.logger.logkv_mean("grad_norm", res[_lib.R_TOTAL_NORM])
+
+    def _after_fused_step(self):
+        if self.opt.grad_mode == _lib.GRAD_ZERO:
+            self._grads_are_zero = True
+        if not self._norm_requested:
+            return
+        self._norm_requested = False
+        host = torch.empty(_lib.R_COUNT, dtype=torch.float64, pin_memory=True)
+        host.copy_(self.opt.engine.results, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._norm_inflight.append((ev, host))
+
+    def _drain_norms(self, block):
+        while self._norm_inflight:
+            ev, host = self._norm_inflight[0]
+            if not block and not ev.query():
+                break
+            ev.synchronize()
+            self.logger.logkv_mean("grad_norm", float(host[_lib.R_LOGGED_NORM]))
+            self._norm_inflight.pop(0)
+
+    def flush_logs(self):
+        """Resolve every pending grad-norm read-back into the logger."""
+        self._drain_norms(block=True)
+
+    def log_step(self):
+        self.logger.logkv("step", self.step + self.resume_step)
+        self.logger.logkv("samples", (self.step + self.resume_step + 1) * self.global_batch)
+
+    # ---- checkpoints (reference :277-355): same file names and layouts ---------
+    def save(self):
+        self.flush_logs()
+        self._save_checkpoint(0, self.master_params)
+        for r, p in zip(self.ema_rate, self.ema_params):
+            self._save_checkpoint(r, p)
+        self._save_opt()
+        dist_util.barrier()
+
+    def _save_checkpoint(self, rate, params):
+        state_dict = self._master_params_to_state_dict(params)
+        if dist_util.get_rank() == 0:
+            self.logger.log(f"saving model {rate}...")
+            n = self.step + self.resume_step
+            filename = f"model_{n:06d}.pt" if not rate else f"ema_{rate}_{n:06d}.pt"
+            path = os.path.join(self.checkpoint_path, filename)
+            print('writing to', path)
+            with open(path, "wb") as f:
+                torch.save(state_dict, f)
+
+    def _save_opt(self):
+        if dist_util.get_rank() == 0:
+            self.logger.log("saving optimizer...")
+            path = os.path.join(self.checkpoint_path, f"opt_{(self.step + self.resume_step):06d}.pt")
+            print('writing to', path)
+            with open(path, "wb") as f:
+                torch.save(self.opt.state_dict(), f)
+
+    def _master_params_to_state_dict(self, master_params, key=None):
+        state_dict = self.model.state_dict()
+        for i, (name, _value) in enumerate(self.model.named_parameters()):
+            assert name in state_dict
+            if key is not None and key == name:
+                return master_params[i]
+            # clone: the checkpoint must not alias (and so serialise) a whole flat buffer
+            state_dict[name] = master_params[i].detach().clone()
+        if key is not None:
+            raise KeyError(key)
+        for name in state_dict:
+            if state_dict[name]._base is not None:
+                state_dict[name] = state_dict[name].detach().clone()
+        return state_dict
+
+    def _state_dict_to_master_params(self, state_dict):
+        return [state_dict[name] for name, _ in self.model.named_parameters()]
+
+    @staticmethod
+    def parse_resume_step_from_filename(filename):
+        """path/to/model_NNNNNN.pt -> NNNNNN"""
+        filename = os.path.basename(filename)
+        assert filename.startswith('model') and filename[-3:] == '.pt', "Invalid model name"
+        return int(filename[-9:-3])
+
+    @staticmethod
+    def find_resume_checkpoint(logger=None):
+        log_dir = (logger or _default_logger).get_current().dir
+        if not log_dir or not os.path.isdir(log_dir):
+            return None
+        names = sorted(s for s in os.listdir(log_dir) if s.endswith(".pt") and s.startswith("model"))
+        return os.path.join(log_dir, names[-1]) if names else None
+
+    @staticmethod
+    def find_ema_checkpoint(main_checkpoint, step, rate):
+        if not main_checkpoint:
+            return None
+        path = os.path.join(os.path.dirname(main_checkpoint), f"ema_{rate}_{step:06d}.pt")
+        return path if os.path.exists(path) else None
+
+    @staticmethod
+    def find_opt_checkpoint(main_checkpoint, step):
+        if not main_checkpoint:
+            return None
+        path = os.path.join(os.path.dirname(main_checkpoint), f"opt_{step:06d}.pt")
+        return path if os.path.exists(path) else None
+
+
+def update_ema(target_params, source_params, rate=0.99):
+    """Move target parameters towards source parameters:
+    ``trg = trg*rate + src*(1-rate)`` (reference utils/trainer.py:360-370).
+
+    When ``target_params`` is one of a TrainLoop's ``ema_params`` lists and the
+    fused step has already advanced it this step, this is a no-op -- so the
+    reference's ``for rate, params in zip(...): update_ema(...)`` loop can stay
+    as written.  Otherwise one kernel per tensor (CUDA tensors only).
+    """
+    entry = _FUSED_EMA_LISTS.get(id(target_params))
+    if entry is not None:
+        opt = entry[0]()
+        k = entry[1]
+        if opt is not None and opt.ema_done[k] and opt.ema_rates[k] == float(rate) \
+                and len(source_params) == len(opt.flat.param_list) \
+                and all(a is b for a, b in zip(source_params, opt.flat.param_list)):
+            opt.ema_done[k] = False
+            return
+    for trg, src in zip(target_params, source_params):
+        _ema_update_kernel(trg.detach(), src.detach(), rate)

@@ -1,0 +1,211 @@
+/*
+ * dpk.h -- C ABI of libdpk, the B200 (sm_100a) data-parallel post-backward
+ * update path: bucketed gradient all-reduce, loss-scale unscale, global L2
+ * grad-norm + clip, AdamW and every Polyak-EMA rate in one fused pass, plus
+ * the loss-aware timestep sampler's gather/update.
+ *
+ * The reference (YAIconvalley/distributed-pipeline) is pure Python and has no
+ * FFI of its own; the seam this library sits under is the method surface of
+ * `TrainLoop` (utils/trainer.py) and the torch objects it holds.  Each entry
+ * point below names the reference lines whose device work it replaces.
+ *
+ * Conventions
+ *   - plain C types only; every pointer named `d_*` or documented "device" is
+ *     a CUDA device pointer, everything else is host memory.
+ *   - every function returns int: 0 ok, >0 a cudaError_t, <0 a DPK_E_* code.
+ *     A human-readable message for the calling thread is kept in
+ *     dpk_last_error().  Nothing aborts, nothing throws.
+ *   - `stream` arguments are `cudaStream_t` passed as void* (NULL = legacy
+ *     default stream).  Calls only enqueue work; the only entry points that
+ *     block the host are the ones whose name ends in `_sync` and
+ *     dpk_create / dpk_destroy / dpk_comm_init.
+ *   - the library never allocates or frees the state buffers: parameters,
+ *     gradients, moments and EMA copies stay owned by the caller (torch), so
+ *     state_dict / deepcopy / torch.save keep working.
+ */
+#ifndef DPK_H_
+#define DPK_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DPK_ABI_VERSION 1
+
+/* error codes (<0); >0 is a cudaError_t */
+#define DPK_E_BADARG  (-1)  /* null / misaligned / out-of-range argument      */
+#define DPK_E_NCCL    (-2)  /* an NCCL call failed (text in dpk_last_error)   */
+#define DPK_E_STATE   (-3)  /* call made in the wrong order / not bound       */
+#define DPK_E_NOMEM   (-4)  /* host allocation failed                         */
+#define DPK_E_LIMIT   (-5)  /* size beyond a documented maximum               */
+
+/* element type of params, grads, both moments and all EMA copies.  The
+ * reference keeps no fp32 master copy (utils/trainer.py:91-92), so all state
+ * shares the model's dtype. */
+#define DPK_F32  0
+#define DPK_BF16 1
+
+#define DPK_MAX_EMA 4
+
+/* what the fused pass leaves in the gradient buffer */
+#define DPK_GRAD_KEEP     0  /* untouched (fastest)                               */
+#define DPK_GRAD_CLIPPED  1  /* g*inv_scale*coef written back, as the reference's
+                                clip_grad_norm_ leaves them (utils/trainer.py:252) */
+#define DPK_GRAD_ZERO     2  /* zeroed: folds TrainLoop._zero_grad (:203-207)     */
+
+/* index into the result block of dpk_grad_norm / dpk_fused_update (doubles) */
+#define DPK_R_TOTAL_NORM   0  /* pre-clip total norm (norm of per-tensor norms)     */
+#define DPK_R_CLIP_COEF    1  /* min(max_norm/(total+1e-6), 1), or 1 if clip off    */
+#define DPK_R_LOGGED_NORM  2  /* sqrt(sum_i sum(g_i^2)) on the grads the step used:
+                                 what TrainLoop._log_grad_norm logs (:265-271)      */
+#define DPK_R_NONFINITE    3  /* 1.0 if any gradient element was inf/nan            */
+#define DPK_R_SKIPPED      4  /* 1.0 if the last fused update predicated itself off */
+#define DPK_R_COUNT        8
+
+typedef struct dpk_handle dpk_handle;
+typedef struct dpk_sampler dpk_sampler;
+
+typedef struct dpk_config {
+  int32_t abi_version;      /* DPK_ABI_VERSION                                  */
+  int32_t dtype;            /* DPK_F32 | DPK_BF16                               */
+  int32_t device;           /* CUDA ordinal the buffers live on                 */
+  int32_t n_segments;       /* parameter tensors (209 for DiffuSeq-base)        */
+  int32_t n_ema;            /* EMA rates, 0..DPK_MAX_EMA                        */
+  int32_t tile_elems;       /* 0 = default; elements per work tile, mult. of 1024 */
+  int64_t n_elems;          /* flat length in elements, padding included        */
+  const int64_t* seg_offsets; /* [n_segments] element offset of each tensor in the
+                                 flat buffers; each a multiple of 16 bytes      */
+  const int64_t* seg_numel; /* [n_segments] elements per tensor (may be 0)      */
+  const double* ema_rates;  /* [n_ema] as parsed by TrainLoop (:72-76)          */
+  double beta1, beta2, eps; /* AdamW defaults of the reference: .9, .999, 1e-8  */
+  int64_t bucket_cap_bytes; /* all-reduce bucket size; reference: 128 MiB (:123) */
+} dpk_config;
+
+/* ---- library ---------------------------------------------------------- */
+
+int dpk_abi_version(void);
+const char* dpk_last_error(void);
+
+/* ---- handle: replaces what TrainLoop.__init__ builds (utils/trainer.py:87-128:
+ * AdamW state, K EMA lists, the DDP reducer's bucket plan) ---------------- */
+
+/* Validates cfg and plans tiles and buckets.  Pure host work: no CUDA call is
+ * made until dpk_bind, so planning can be inspected on a machine without a GPU. */
+int dpk_create(dpk_handle** out, const dpk_config* cfg);
+int dpk_destroy(dpk_handle* h);
+
+/* Borrow the caller's flat device buffers (each n_elems long, 16-byte aligned,
+ * same dtype).  d_emas has cfg.n_ema entries.  Gaps between tensors are never
+ * read as data nor modified.  The first call also allocates the library's own
+ * small device scratch (tile table, per-tile partial sums, result block). */
+int dpk_bind(dpk_handle* h, void* d_params, void* d_grads, void* d_exp_avg,
+             void* d_exp_avg_sq, void* const* d_emas);
+
+/* ---- communicator: the process group itself is still created by
+ * basic_utils/dist_util.py:57-85; the caller ships the 128-byte id from rank 0
+ * to every rank through that group and then calls dpk_comm_init. ----------- */
+
+int dpk_comm_unique_id(void* out128);
+int dpk_comm_init(dpk_handle* h, const void* id128, int32_t world_size, int32_t rank);
+int dpk_world_size(const dpk_handle* h);
+
+/* ---- gradient all-reduce: replaces torch DDP's reducer as configured at
+ * utils/trainer.py:118-125 (bucket_cap_mb=128; average = pre-multiply by 1/W
+ * then SUM), in place on the flat gradient buffer. -------------- */
+
+int dpk_num_buckets(const dpk_handle* h);
+/* bucket b covers flat elements [*start, *start + *count); bucket 0 is the
+ * tail of the buffer (gradients become ready in reverse definition order). */
+int dpk_bucket_range(const dpk_handle* h, int32_t b, int64_t* start, int64_t* count);
+/* All gradients of bucket b have been produced on `producer_stream`: enqueue
+ * its all-reduce on the library's communication stream.  Thread-safe (it is
+ * called from autograd's engine thread). */
+int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream);
+/* Make `consumer_stream` wait for every all-reduce enqueued so far. */
+int dpk_wait_allreduce(dpk_handle* h, void* consumer_stream);
+/* One coalesced broadcast of params (+ every EMA copy if include_ema) from
+ * `root`: replaces DDP's constructor broadcast and the per-tensor loop of
+ * basic_utils/dist_util.py:141-152. */
+int dpk_broadcast_state(dpk_handle* h, int32_t root, int32_t include_ema, void* stream);
+
+/* ---- the update ------------------------------------------------------- */
+
+/* TrainLoop._zero_grad (utils/trainer.py:203-207) as one fill. */
+int dpk_zero_grads(dpk_handle* h, void* stream);
+
+/* Pass 1: TrainLoop.grad_clip -> torch.nn.utils.clip_grad_norm_
+ * (utils/trainer.py:246-255; torch nn/utils/clip_grad.py:92-108,165-174) and the
+ * non-finite test of the upstream loss-scale path.  Reads g once; gradients are
+ * taken as g*inv_scale.  max_norm <= 0 disables clipping (coef = 1).  Results
+ * land in the device result block; nothing is written to g. */
+int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream);
+
+/* Pass 2: TrainLoop.optimize after the clip (utils/trainer.py:240-244):
+ * AdamW.step() (torch optim/adam.py:683-800) and update_ema for every rate
+ * (utils/trainer.py:360-370), one read and one write per state element.
+ *   lr            this step's learning rate (after _anneal_lr, :257-263)
+ *   adam_step     AdamW's step count for this update (1 on the first call)
+ *   use_clip_coef 1: scale g by the coefficient the last dpk_grad_norm left in
+ *                 the result block; 0: coefficient 1
+ *   skip_if_nonfinite 1: do nothing (and set R_SKIPPED) when the last
+ *                 dpk_grad_norm saw inf/nan -- the loss-scale "skip step"
+ *   grad_mode     DPK_GRAD_*
+ * Also accumulates sum(g^2) of the gradients it used, so R_LOGGED_NORM is
+ * valid afterwards even when dpk_grad_norm was not called. */
+int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
+                     double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite,
+                     int32_t grad_mode, void* stream);
+
+/* Device address of the result block (DPK_R_COUNT doubles). */
+int dpk_result_ptr(dpk_handle* h, void** d_out);
+/* Copy the result block to `out[DPK_R_COUNT]` and wait for it: the single host
+ * read that replaces the 209 .item() calls of TrainLoop._log_grad_norm. */
+int dpk_read_result_sync(dpk_handle* h, double* out, void* stream);
+/* Per-tensor L2 norms of the last dpk_grad_norm (n_segments doubles, device). */
+int dpk_segment_norms_ptr(dpk_handle* h, void** d_out);
+
+/* Stand-alone update_ema(target, source, rate) (utils/trainer.py:360-370) on
+ * caller-supplied contiguous device arrays of `n` elements, for callers that
+ * use the module-level function outside optimize(). */
+int dpk_ema_update(void* d_target, const void* d_source, int64_t n, int32_t dtype,
+                   double rate, void* stream);
+
+/* ---- instrumentation (bench.py's roofline line; nothing in the reference
+ * corresponds: its logger.profile_kv, basic_utils/logger.py:296-320, times the
+ * host only).  With timing enabled every dpk_fused_update / dpk_grad_norm
+ * brackets its streaming kernel -- that kernel alone, not the small reductions
+ * behind it -- with CUDA events on the caller's stream, up to DPK_TIMING_SLOTS
+ * launches between two reads. ---------------------------------------------- */
+
+#define DPK_TIMING_SLOTS 256
+int dpk_timing_enable(dpk_handle* h, int32_t on);
+/* Waits for the recorded events, writes up to `cap` durations (ms, oldest
+ * first) for kernel `which` (0 = fused update, 1 = sum-of-squares) and clears
+ * them. */
+int dpk_timing_read_sync(dpk_handle* h, int32_t which, float* ms_out, int32_t cap, int32_t* n_out);
+/* Kernels this handle has launched since creation. */
+int dpk_launch_count(const dpk_handle* h, int64_t* out);
+
+/* ---- loss-aware timestep sampler.  Absent from the reference;
+ * semantics are upstream improved-diffusion resample.py
+ * (LossSecondMomentResampler + LossAwareSampler.update_with_local_losses). -- */
+
+int dpk_sampler_create(dpk_sampler** out, int32_t device, int32_t n_timesteps,
+                       int32_t history_per_term, double uniform_prob, int32_t max_local_batch);
+int dpk_sampler_destroy(dpk_sampler* s);
+/* Gather every rank's (timestep, loss) records (rank-major, batch order) over
+ * the handle's communicator (h may be NULL or single-rank: local only) and
+ * apply update_with_all_losses.  d_ts int64[n_local], d_losses float[n_local]. */
+int dpk_sampler_update(dpk_sampler* s, dpk_handle* h, const int64_t* d_ts,
+                       const float* d_losses, int32_t n_local, void* stream);
+/* weights() into a device array of n_timesteps doubles. */
+int dpk_sampler_weights(dpk_sampler* s, double* d_weights, void* stream);
+/* Device views of the state, for checkpointing and tests. */
+int dpk_sampler_state_ptrs(dpk_sampler* s, void** d_history, void** d_counts);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DPK_H_ */
