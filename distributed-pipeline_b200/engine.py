@@ -37,6 +37,8 @@ class Engine:
         if device.type != "cuda":
             raise RuntimeError(
                 "the B200 update path has no CPU implementation: parameters must live on a CUDA device")
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
         if len(ema_rates) > _lib.MAX_EMA:
             raise ValueError(f"at most {_lib.MAX_EMA} EMA rates are supported, got {len(ema_rates)}")
         self.lib = _lib.lib()
@@ -53,7 +55,7 @@ class Engine:
         rates = (C.c_double * max(len(self.ema_rates), 1))(*self.ema_rates)
         cfg = _lib.Config(
             abi_version=_lib.ABI_VERSION, dtype=dtype_code(dtype),
-            device=device.index if device.index is not None else torch.cuda.current_device(),
+            device=device.index,
             n_segments=n_seg, n_ema=len(self.ema_rates), tile_elems=tile_elems, n_elems=layout.n_elems,
             seg_offsets=offs, seg_numel=nums, ema_rates=rates,
             beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, bucket_cap_bytes=bucket_cap_bytes)

@@ -45,7 +45,8 @@ class BucketReducer:
         if missing:
             raise RuntimeError(f"bucket plan does not cover parameters {sorted(missing)[:5]}...")
         self._pending = [len(idxs) for idxs in self.bucket_params]
-        self._fired = [False] * len(ranges)
+        self._ready = [False] * len(ranges)
+        self._next = 0
         self._handles = []
         for i, p in enumerate(flat.param_list):
             if p.requires_grad:
@@ -57,31 +58,37 @@ class BucketReducer:
         def hook(param):
             if not self.armed or self.engine.world_size <= 1:
                 return
+            launch = []
             with self._lock:
                 if not self._callback_queued:
                     # like DDP's reducer: finish once this backward pass is over
                     self._callback_queued = True
                     torch.autograd.Variable._execution_engine.queue_callback(self.finish)
                 self._pending[b] -= 1
-                fire = self._pending[b] == 0 and not self._fired[b]
-                if fire:
-                    self._fired[b] = True
-            if fire:
+                if self._pending[b] == 0:
+                    self._ready[b] = True
+                # Collectives must be issued in the same order on every rank, whatever
+                # order the hooks happen to run in: buckets launch strictly by index,
+                # a ready bucket waiting for its predecessors (DDP's next_bucket rule).
+                while self._next < len(self._ready) and self._ready[self._next]:
+                    launch.append(self._next)
+                    self._next += 1
+            for nb in launch:
                 # runs on autograd's engine thread; the current stream there is
-                # the one the gradient was produced on
-                self.engine.bucket_ready(b)
+                # the one the gradients were produced on
+                self.engine.bucket_ready(nb)
         return hook
 
     def finish(self):
         """After backward(): launch buckets whose parameters did not all receive
         a gradient, make the current stream wait for every all-reduce, re-arm."""
         if self.armed and self.engine.world_size > 1:
-            for b, fired in enumerate(self._fired):
-                if not fired:
-                    self.engine.bucket_ready(b)
+            for b in range(self._next, len(self._ready)):
+                self.engine.bucket_ready(b)
             self.engine.wait_allreduce()
         self._pending = [len(idxs) for idxs in self.bucket_params]
-        self._fired = [False] * len(self._fired)
+        self._ready = [False] * len(self._ready)
+        self._next = 0
         self._callback_queued = False
         self.armed = False
 

@@ -1,0 +1,135 @@
+"""BASELINE.json's full sizes (DiffuSeq-base: 209 tensors, 91 225 274 params; and
+a >2^31-element flat sweep point), checked through size-independent properties
+and against torch-CUDA eager running the reference's op sequence."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from distributed_pipeline_b200 import _lib
+from distributed_pipeline_b200.synthetic import diffuseq_shapes, numel
+from helpers import FlatProblem, assert_bits_equal, rel_err, to_np
+from oracle.torch_port import ReferenceUpdatePort
+
+pytestmark = pytest.mark.gpu
+
+
+def _pick(pb, flat):
+    return torch.cat([flat[o:o + n] for o, n in zip(pb.layout.offsets, pb.layout.numels)])
+
+
+def _port_for(pb, shapes, rates, wd, clip):
+    tensors = [torch.nn.Parameter(pb.p[o:o + n].clone().view(s))
+               for o, n, s in zip(pb.layout.offsets, pb.layout.numels, shapes)]
+    return ReferenceUpdatePort(tensors, lr=1e-4, ema_rates=rates, weight_decay=wd, gradient_clipping=clip)
+
+
+@pytest.mark.parametrize("dtype,rates,clip", [(torch.float32, [0.9999], -1.0), (torch.bfloat16, [0.9999, 0.999], 1.0)])
+def test_diffuseq_base_matches_torch_cuda(dtype, rates, clip):
+    shapes = diffuseq_shapes()
+    numels = [numel(s) for s in shapes]
+    assert len(shapes) == 209 and sum(numels) == 91225274
+    pb = FlatProblem(numels, dtype, rates, seed=1, mirror=False)
+    port = _port_for(pb, shapes, rates, 0.0, clip)
+    for step in (1, 2, 3):
+        pb.new_grads(std=1e-3, poison_padding=True)
+        for t, o, n in zip(port.params, pb.layout.offsets, pb.layout.numels):
+            t.grad = pb.g[o:o + n].clone().view(t.shape)
+        port.optimize()
+        if clip > 0:
+            pb.engine.grad_norm(1.0, clip)
+        pb.engine.fused_update(1e-4, 0.0, step, use_clip_coef=clip > 0, grad_mode=_lib.GRAD_KEEP)
+        res = pb.engine.read_results_sync()
+        if dtype == torch.float32:
+            assert rel_err(res[_lib.R_LOGGED_NORM], port.last_logged_norm) < 1e-5
+        else:
+            assert rel_err(res[_lib.R_TOTAL_NORM], float(port.last_total_norm)) <= 2 ** -7
+            assert rel_err(res[_lib.R_LOGGED_NORM], port.last_logged_norm) < 4e-3
+    cat = lambda ts: torch.cat([t.detach().reshape(-1) for t in ts])
+    pairs = {"p": (_pick(pb, pb.p), cat(port.params)),
+             "m": (_pick(pb, pb.m), cat([port.opt.state[p]["exp_avg"] for p in port.params])),
+             "v": (_pick(pb, pb.v), cat([port.opt.state[p]["exp_avg_sq"] for p in port.params]))}
+    for k, e in enumerate(pb.emas):
+        pairs[f"ema{k}"] = (_pick(pb, e), cat(port.ema_params[k]))
+    for name, (a, b) in pairs.items():
+        if dtype == torch.float32:
+            assert torch.equal(a, b), f"{name}: {(a != b).float().mean().item():.3g} of elements differ"
+        else:
+            ulp = (a.view(torch.int16).int() - b.view(torch.int16).int()).abs()
+            # clip coefficient is a bf16 value; if ours lands on the neighbouring bf16
+            # the whole gradient moves by one ulp -- still ulp-level
+            assert int(ulp.max()) <= 8, (name, int(ulp.max()), float((ulp != 0).float().mean()))
+
+
+def test_fullsize_properties_fp32():
+    shapes = diffuseq_shapes()
+    numels = [numel(s) for s in shapes]
+    pb = FlatProblem(numels, torch.float32, [0.9999], seed=2, mirror=False)
+    pb.new_grads(std=1e-3, poison_padding=False)
+    g0 = pb.g.clone()
+    state0 = [t.clone() for t in (pb.p, pb.m, pb.v, pb.emas[0])]
+
+    # (1) the norm agrees with an fp64 reduction of the same buffer
+    pb.engine.grad_norm(1.0, 1.0)
+    res = pb.engine.read_results_sync()
+    truth = float(torch.linalg.vector_norm(g0.double()))
+    assert rel_err(res[_lib.R_TOTAL_NORM], truth) < 1e-6
+    assert rel_err(res[_lib.R_CLIP_COEF], min(1.0, 1.0 / (truth + 1e-6))) < 1e-6
+
+    # (2) unscale is exact for power-of-two scales: (g*2^k, 2^-k) == (g, 1), bit for bit
+    pb.engine.fused_update(1e-4, 0.01, 1, grad_mode=_lib.GRAD_KEEP)
+    ref = [t.clone() for t in (pb.p, pb.m, pb.v, pb.emas[0])]
+    for t, s in zip((pb.p, pb.m, pb.v, pb.emas[0]), state0):
+        t.copy_(s)
+    pb.g.mul_(2.0 ** 12)
+    pb.engine.fused_update(1e-4, 0.01, 1, inv_scale=2.0 ** -12, grad_mode=_lib.GRAD_CLIPPED)
+    for t, r, name in zip((pb.p, pb.m, pb.v, pb.emas[0]), ref, "pmve"):
+        assert torch.equal(t, r), name
+    assert torch.equal(pb.g, g0)  # CLIPPED mode wrote the unscaled gradient back
+
+    # (3) lr = 0, wd = 0: parameters are a fixed point; EMA of a fixed point that
+    #     equals it stays within one rounding of it
+    before = pb.p.clone()
+    pb.engine.fused_update(0.0, 0.0, 2, grad_mode=_lib.GRAD_ZERO)
+    assert torch.equal(pb.p, before)
+    assert not pb.g.any()  # ZERO mode
+
+    # (4) zero gradients: moments decay exactly by beta; nothing else moves them
+    m0, v0 = pb.m.clone(), pb.v.clone()
+    pb.engine.fused_update(0.0, 0.0, 3, grad_mode=_lib.GRAD_KEEP)
+    assert torch.equal(pb.m, torch.addcmul(m0, m0, torch.full_like(m0, -1.0), value=float(np.float32(1 - 0.9))))
+    assert torch.equal(pb.v, v0 * float(np.float32(0.999)))
+
+
+def test_more_than_2_31_elements():
+    """Sweep point ~2 B params as one flat tensor: 64-bit offsets in tiles and kernels."""
+    n = 2 ** 31 + 4099
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60 * 2 ** 30:
+        pytest.skip("needs ~45 GB of free device memory")
+    from distributed_pipeline_b200.engine import Engine
+    from distributed_pipeline_b200.flat import FlatLayout
+    lay = FlatLayout.from_numels([n], 4)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    p = torch.empty(lay.n_elems, device=dev).normal_(0, 0.02)
+    g = torch.empty(lay.n_elems, device=dev).normal_(0, 1e-3)
+    m = torch.zeros(lay.n_elems, device=dev)
+    v = torch.zeros(lay.n_elems, device=dev)
+    eng = Engine(lay, torch.float32, dev, [])
+    eng.bind(p, g, m, v, [])
+    lo, hi = n - 5000, n          # the tail lives beyond 2^31
+    mid = slice(2 ** 31 - 2048, 2 ** 31 + 2048)
+    host = {}
+    for name, sl in (("tail", slice(lo, hi)), ("mid", mid), ("head", slice(0, 4096))):
+        host[name] = [t[sl].cpu().numpy().copy() for t in (p, g, m, v)]
+    eng.grad_norm(1.0, 1.0)
+    eng.fused_update(1e-3, 0.01, 1, use_clip_coef=True, grad_mode=_lib.GRAD_KEEP)
+    res = eng.read_results_sync()
+    # sum of squares of N(0, 1e-3^2): norm ~ 1e-3*sqrt(n)
+    assert rel_err(res[_lib.R_TOTAL_NORM], 1e-3 * np.sqrt(n)) < 1e-3
+    for name, sl in (("tail", slice(lo, hi)), ("mid", mid), ("head", slice(0, 4096))):
+        hp, hg, hm, hv = host[name]
+        oracle.adamw_ema_step(oracle.F32, hp, hg, hm, hv, [], [], 1e-3, 0.01, 1, coef=res[_lib.R_CLIP_COEF])
+        assert_bits_equal(p[sl].cpu().numpy(), hp, f"p {name}")
+        assert_bits_equal(m[sl].cpu().numpy(), hm, f"m {name}")
+        assert_bits_equal(v[sl].cpu().numpy(), hv, f"v {name}")

@@ -67,9 +67,11 @@ def test_fp32_matches_torch_cuda(clip, wd, learning_steps, n_steps):
     stats = {}
     for name, (a, b) in _gather(pb, port).items():
         a64, b64 = a.double().cpu().numpy(), b.double().cpu().numpy()
-        # relative to the tensor's scale for entries that sit next to zero
-        scale = np.abs(b64).max()
-        err = np.abs(a64 - b64) / np.maximum(np.abs(b64), 1e-3 * scale)
+        # north_star: relative 1e-6 after N steps.  Entries that pass through zero
+        # have no meaningful relative error, hence the usual allclose form with the
+        # absolute floor tied to the tensor's own scale: |a-b| <= 1e-6*(|b| + rms(b)).
+        rms = float(np.sqrt(np.mean(b64 ** 2)))
+        err = np.abs(a64 - b64) / (np.abs(b64) + rms)
         stats[name] = (float(err.max()), float((a64 != b64).mean()))
         assert err.max() < 1e-6, (name, stats[name])
     print(f"\nfp32 clip={clip} steps={n_steps}: max rel err / fraction of elements not bit-equal: {stats}")
