@@ -21,29 +21,61 @@ struct SamplerRecord {
 static_assert(sizeof(SamplerRecord) == 16, "packed record is 16 bytes");
 
 // numpy's pairwise sum for a contiguous fp64 run (PW_BLOCKSIZE = 128).
-__device__ double np_pairwise_sum(const double* a, int n) {
+// Leaf: fewer than 8 values are added left to right; otherwise eight running
+// lanes, combined as ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)), then the tail.
+__device__ double np_leaf_sum(const double* a, int n) {
   if (n < 8) {
-    double res = 0.0;  // numpy starts from a[0] with -0.0 semantics aside; values here are >= 0
+    double res = 0.0;
     for (int i = 0; i < n; ++i) res = __dadd_rn(res, a[i]);
     return res;
   }
-  if (n <= 128) {
-    double r[8];
+  double r[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) r[j] = a[j];
-    int i;
-    for (i = 8; i < n - (n % 8); i += 8) {
+  for (int j = 0; j < 8; ++j) r[j] = a[j];
+  int i;
+  for (i = 8; i < n - (n % 8); i += 8) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], a[i + j]);
-    }
-    double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
-                           __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
-    for (; i < n; ++i) res = __dadd_rn(res, a[i]);
-    return res;
+    for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], a[i + j]);
   }
-  int n2 = n / 2;
-  n2 -= n2 % 8;
-  return __dadd_rn(np_pairwise_sum(a, n2), np_pairwise_sum(a + n2, n - n2));
+  double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                         __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+  for (; i < n; ++i) res = __dadd_rn(res, a[i]);
+  return res;
+}
+
+// Above 128 values numpy splits at n/2 rounded down to a multiple of 8 and adds
+// the two halves' sums.  Written with an explicit stack: device recursion would
+// depend on the per-thread stack limit.
+__device__ double np_pairwise_sum(const double* a, int n) {
+  struct Frame { int off, n, stage; double left; };
+  Frame st[32];
+  int sp = 0;
+  st[0].off = 0; st[0].n = n; st[0].stage = 0; st[0].left = 0.0;
+  double ret = 0.0;
+  while (sp >= 0) {
+    Frame& f = st[sp];
+    if (f.n <= 128) {
+      ret = np_leaf_sum(a + f.off, f.n);
+      --sp;
+      continue;
+    }
+    int n2 = f.n / 2;
+    n2 -= n2 % 8;
+    if (f.stage == 0) {
+      f.stage = 1;
+      ++sp;
+      st[sp].off = f.off; st[sp].n = n2; st[sp].stage = 0; st[sp].left = 0.0;
+    } else if (f.stage == 1) {
+      f.left = ret;
+      f.stage = 2;
+      ++sp;
+      st[sp].off = f.off + n2; st[sp].n = f.n - n2; st[sp].stage = 0; st[sp].left = 0.0;
+    } else {
+      ret = __dadd_rn(f.left, ret);
+      --sp;
+    }
+  }
+  return ret;
 }
 
 // Pack this rank's records into its slot of the gather buffer.
