@@ -22,6 +22,7 @@ MAX_EMA = 4
 GRAD_KEEP, GRAD_CLIPPED, GRAD_ZERO = 0, 1, 2
 R_TOTAL_NORM, R_CLIP_COEF, R_LOGGED_NORM, R_NONFINITE, R_SKIPPED, R_COUNT = 0, 1, 2, 3, 4, 8
 E_BADARG, E_NCCL, E_STATE, E_NOMEM, E_LIMIT = -1, -2, -3, -4, -5
+STATIC_MAX_ELEMS = 536870912
 
 
 class DpkError(RuntimeError):
@@ -73,6 +74,7 @@ SIGNATURES = {
     "dpk_result_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),
     "dpk_read_result_sync": (C.c_int, [_VP, C.POINTER(C.c_double), _VP]),
     "dpk_segment_norms_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "dpk_grad_norm_static": (C.c_int, [_VP, C.c_int64, C.c_int32, C.c_double, C.c_double, _VP, _VP]),
     "dpk_timing_enable": (C.c_int, [_VP, C.c_int32]),
     "dpk_timing_read_sync": (C.c_int, [_VP, C.c_int32, C.POINTER(C.c_float), C.c_int32, C.POINTER(C.c_int32)]),
     "dpk_launch_count": (C.c_int, [_VP, C.POINTER(C.c_int64)]),

@@ -172,6 +172,34 @@ int dpk_segment_norms_ptr(dpk_handle* h, void** d_out);
 int dpk_ema_update(void* d_target, const void* d_source, int64_t n, int32_t dtype,
                    double rate, void* stream);
 
+/* ---- allocation-free norm.  No counterpart in the reference: it exists for
+ * callers of THIS library that cannot allocate device memory -- code running
+ * mid-step on a GPU whose free memory already belongs to the framework's caching
+ * allocator, where a raw cudaMalloc (which dpk_create/dpk_bind perform) may fail
+ * outright, fragments what is left and synchronises the whole device.
+ *
+ * Computes what dpk_grad_norm computes for a layout of ONE tensor of n elements
+ * (same arithmetic, same reduction order, same bits): the L2 norm of
+ * d_grads*inv_scale, the clip coefficient for max_norm (<= 0: coefficient 1) and
+ * the non-finite flag, written to d_out[DPK_R_TOTAL_NORM], d_out[DPK_R_CLIP_COEF]
+ * and d_out[DPK_R_NONFINITE]; d_out is a caller-owned device array of
+ * DPK_R_COUNT doubles, its other entries are left alone.  d_grads must be
+ * 16-byte aligned; dtype is DPK_F32 or DPK_BF16.  Runs on the current device.
+ *
+ * The scratch (per-tile partial sums) is a fixed array inside the library's
+ * device image, 512 KiB per GPU for the life of the process; hence the limit:
+ * n > DPK_STATIC_MAX_ELEMS returns DPK_E_LIMIT.  The call makes no cudaMalloc /
+ * cudaFree and uses no allocating library routine.  The first call on each
+ * device resolves the scratch address (cudaGetSymbolAddress): make that call
+ * before starting any stream capture.  All calls on a device share the one
+ * scratch, which still holds the previous call's values when the next begins
+ * (every word a call reads it has first rewritten, so none needs clearing);
+ * two calls whose kernels overlap on the GPU -- different streams without an
+ * ordering between them -- race on it and return garbage. */
+#define DPK_STATIC_MAX_ELEMS 536870912
+int dpk_grad_norm_static(const void* d_grads, int64_t n, int32_t dtype, double inv_scale,
+                         double max_norm, double* d_out, void* stream);
+
 /* ---- instrumentation (bench.py's roofline line; nothing in the reference
  * corresponds: its logger.profile_kv, basic_utils/logger.py:296-320, times the
  * host only).  With timing enabled every dpk_fused_update / dpk_grad_norm
