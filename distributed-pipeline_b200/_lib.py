@@ -65,12 +65,18 @@ SIGNATURES = {
     "dpk_num_buckets": (C.c_int, [_VP]),
     "dpk_bucket_range": (C.c_int, [_VP, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "dpk_bucket_ready": (C.c_int, [_VP, C.c_int32, _VP]),
+    "dpk_wait_bucket": (C.c_int, [_VP, C.c_int32, _VP]),
     "dpk_wait_allreduce": (C.c_int, [_VP, _VP]),
     "dpk_broadcast_state": (C.c_int, [_VP, C.c_int32, C.c_int32, _VP]),
     "dpk_zero_grads": (C.c_int, [_VP, _VP]),
     "dpk_grad_norm": (C.c_int, [_VP, C.c_double, C.c_double, _VP]),
     "dpk_fused_update": (C.c_int, [_VP, C.c_double, C.c_double, C.c_int64, C.c_double, C.c_int32,
                                     C.c_int32, C.c_int32, _VP]),
+    "dpk_grad_norm_bucket": (C.c_int, [_VP, C.c_int32, C.c_double, _VP]),
+    "dpk_grad_norm_finish": (C.c_int, [_VP, C.c_double, _VP]),
+    "dpk_fused_update_bucket": (C.c_int, [_VP, C.c_int32, C.c_double, C.c_double, C.c_int64, C.c_double, C.c_int32,
+                                           C.c_int32, C.c_int32, _VP]),
+    "dpk_fused_update_finish": (C.c_int, [_VP, C.c_int32, _VP]),
     "dpk_result_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),
     "dpk_read_result_sync": (C.c_int, [_VP, C.POINTER(C.c_double), _VP]),
     "dpk_segment_norms_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),

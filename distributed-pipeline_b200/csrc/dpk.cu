@@ -164,21 +164,23 @@ static int launch_segment_reduce(dpk_handle* h, const TilePartial* partials, cud
 // ---- pass 2 ---------------------------------------------------------------
 
 template <typename T, int K, int GM>
-static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef, int skip,
-                              cudaStream_t st) {
-  const int n_tiles = (int)h->tiles.size();
-  if (n_tiles == 0) return 0;
+static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int tile_begin,
+                              int tile_end, cudaStream_t st) {
+  const int n_tiles = tile_end - tile_begin;
+  if (n_tiles <= 0) return 0;
   UpdateArgs<T, K> a;
   a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
   for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
   a.tiles = h->d_tiles;
-  a.n_tiles = n_tiles;
+  a.tile_begin = tile_begin;
+  a.tile_end = tile_end;
   a.partials = h->d_partials_post;
   a.results = h->d_results;
   a.use_clip_coef = use_coef;
   a.skip_if_nonfinite = skip;
   a.s = sc;
-  auto kern = fused_update_kernel<T, K, GM, 2>;
+  // vectors in flight per thread and array: 2 x 4 fp32 elements, 1 x 8 bf16 elements
+  auto kern = fused_update_kernel<T, K, GM, (sizeof(T) == 4 ? 2 : 1)>;
   int grid = 0;
   if (int rc = grid_for(kern, n_tiles, h->sm_count, &grid)) return rc;
   {
@@ -191,24 +193,24 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
 }
 
 template <typename T, int K>
-static int launch_update_gm(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int gm,
+static int launch_update_gm(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int gm, int tb, int te,
                             cudaStream_t st) {
   switch (gm) {
-    case DPK_GRAD_KEEP: return launch_update_impl<T, K, DPK_GRAD_KEEP>(h, sc, use_coef, skip, st);
-    case DPK_GRAD_CLIPPED: return launch_update_impl<T, K, DPK_GRAD_CLIPPED>(h, sc, use_coef, skip, st);
-    default: return launch_update_impl<T, K, DPK_GRAD_ZERO>(h, sc, use_coef, skip, st);
+    case DPK_GRAD_KEEP: return launch_update_impl<T, K, DPK_GRAD_KEEP>(h, sc, use_coef, skip, tb, te, st);
+    case DPK_GRAD_CLIPPED: return launch_update_impl<T, K, DPK_GRAD_CLIPPED>(h, sc, use_coef, skip, tb, te, st);
+    default: return launch_update_impl<T, K, DPK_GRAD_ZERO>(h, sc, use_coef, skip, tb, te, st);
   }
 }
 
 template <typename T>
-static int launch_update(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int gm,
+static int launch_update(dpk_handle* h, const StepScalars& sc, int use_coef, int skip, int gm, int tb, int te,
                          cudaStream_t st) {
   switch (h->n_ema) {
-    case 0: return launch_update_gm<T, 0>(h, sc, use_coef, skip, gm, st);
-    case 1: return launch_update_gm<T, 1>(h, sc, use_coef, skip, gm, st);
-    case 2: return launch_update_gm<T, 2>(h, sc, use_coef, skip, gm, st);
-    case 3: return launch_update_gm<T, 3>(h, sc, use_coef, skip, gm, st);
-    default: return launch_update_gm<T, 4>(h, sc, use_coef, skip, gm, st);
+    case 0: return launch_update_gm<T, 0>(h, sc, use_coef, skip, gm, tb, te, st);
+    case 1: return launch_update_gm<T, 1>(h, sc, use_coef, skip, gm, tb, te, st);
+    case 2: return launch_update_gm<T, 2>(h, sc, use_coef, skip, gm, tb, te, st);
+    case 3: return launch_update_gm<T, 3>(h, sc, use_coef, skip, gm, tb, te, st);
+    default: return launch_update_gm<T, 4>(h, sc, use_coef, skip, gm, tb, te, st);
   }
 }
 
@@ -221,6 +223,7 @@ static void free_handle(dpk_handle* h) {
   if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
   if (h->ev_ready) cudaEventDestroy(h->ev_ready);
   if (h->ev_done) cudaEventDestroy(h->ev_done);
+  for (cudaEvent_t e : h->ev_bucket_done) cudaEventDestroy(e);
   cudaFree(h->d_tiles);
   cudaFree(h->d_seg_tile_begin);
   cudaFree(h->d_partials_pre);
@@ -261,6 +264,12 @@ static int ensure_device_state(dpk_handle* h) {
   DPK_CUDA(cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, hi));
   DPK_CUDA(cudaEventCreateWithFlags(&h->ev_ready, cudaEventDisableTiming));
   DPK_CUDA(cudaEventCreateWithFlags(&h->ev_done, cudaEventDisableTiming));
+  for (size_t b = 0; b < h->buckets.size(); ++b) {
+    cudaEvent_t e = nullptr;
+    DPK_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    h->ev_bucket_done.push_back(e);
+  }
+  h->bucket_pending.assign(h->buckets.size(), 0);
   // last: d_results doubles as the "initialised" marker
   double* res = nullptr;
   DPK_CUDA(cudaMalloc(&res, DPK_R_COUNT * sizeof(double)));
@@ -487,8 +496,21 @@ int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream) {
   // reducer's semantics, in place, no copy-in / copy-out.
   DPK_NCCL(api->AllReduce(base, base, (size_t)bk.count, h->dtype == DPK_F32 ? ncclFloat32 : ncclBfloat16,
                           ncclAvg, h->comm, h->comm_stream));
+  DPK_CUDA(cudaEventRecord(h->ev_bucket_done[b], h->comm_stream));
   DPK_CUDA(cudaEventRecord(h->ev_done, h->comm_stream));
+  h->bucket_pending[b] = 1;
   h->any_enqueued = true;
+  return 0;
+}
+
+int dpk_wait_bucket(dpk_handle* h, int32_t b, void* consumer_stream) {
+  if (!h || b < 0 || b >= (int)h->buckets.size()) { set_error("dpk_wait_bucket: bad bucket"); return DPK_E_BADARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  if (b < (int)h->bucket_pending.size() && h->bucket_pending[b]) {
+    DPK_CUDA(cudaStreamWaitEvent((cudaStream_t)consumer_stream, h->ev_bucket_done[b], 0));
+    h->bucket_pending[b] = 0;
+  }
   return 0;
 }
 
@@ -499,6 +521,7 @@ int dpk_wait_allreduce(dpk_handle* h, void* consumer_stream) {
   if (h->any_enqueued) {
     DPK_CUDA(cudaStreamWaitEvent((cudaStream_t)consumer_stream, h->ev_done, 0));
     h->any_enqueued = false;
+    std::fill(h->bucket_pending.begin(), h->bucket_pending.end(), 0);
     if (h->comm) {
       const NcclApi* api = nccl_api();
       ncclResult_t async = ncclSuccess;
@@ -540,16 +563,35 @@ int dpk_zero_grads(dpk_handle* h, void* stream) {
   return 0;
 }
 
-int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream) {
-  if (!h) { set_error("dpk_grad_norm: null handle"); return DPK_E_BADARG; }
+static int bucket_tiles(const dpk_handle* h, int32_t bucket, int* tb, int* te, const char* who) {
+  if (bucket < 0) {
+    *tb = 0;
+    *te = (int)h->tiles.size();
+    return 0;
+  }
+  if (bucket >= (int)h->buckets.size()) { set_error("%s: bad bucket %d", who, bucket); return DPK_E_BADARG; }
+  *tb = h->buckets[bucket].tile_begin;
+  *te = h->buckets[bucket].tile_end;
+  return 0;
+}
+
+int dpk_grad_norm_bucket(dpk_handle* h, int32_t bucket, double inv_scale, void* stream) {
+  if (!h) { set_error("dpk_grad_norm_bucket: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_grad_norm: buffers not bound"); return DPK_E_STATE; }
+  int tb = 0, te = 0;
+  if (int rc = bucket_tiles(h, bucket, &tb, &te, "dpk_grad_norm_bucket")) return rc;
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  return (h->dtype == DPK_F32) ? launch_sumsq<float>(h, tb, te, (float)inv_scale, st)
+                               : launch_sumsq<__nv_bfloat16>(h, tb, te, (float)inv_scale, st);
+}
+
+int dpk_grad_norm_finish(dpk_handle* h, double max_norm, void* stream) {
+  if (!h) { set_error("dpk_grad_norm_finish: null handle"); return DPK_E_BADARG; }
   if (!h->bound) { set_error("dpk_grad_norm: buffers not bound"); return DPK_E_STATE; }
   DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
-  const int n_tiles = (int)h->tiles.size();
-  int rc = (h->dtype == DPK_F32) ? launch_sumsq<float>(h, 0, n_tiles, (float)inv_scale, st)
-                                 : launch_sumsq<__nv_bfloat16>(h, 0, n_tiles, (float)inv_scale, st);
-  if (rc) return rc;
-  if ((rc = launch_segment_reduce(h, h->d_partials_pre, st))) return rc;
+  if (int rc = launch_segment_reduce(h, h->d_partials_pre, st)) return rc;
   if (h->dtype == DPK_F32)
     finalize_norm_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->d_seg_bad, h->n_seg, (float)max_norm,
                                                         h->d_seg_norms, h->d_results);
@@ -561,12 +603,20 @@ int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream
   return 0;
 }
 
-int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step, double inv_scale,
-                     int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode, void* stream) {
+int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream) {
+  if (int rc = dpk_grad_norm_bucket(h, -1, inv_scale, stream)) return rc;
+  return dpk_grad_norm_finish(h, max_norm, stream);
+}
+
+int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double weight_decay, int64_t adam_step,
+                            double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
+                            void* stream) {
   if (!h) { set_error("dpk_fused_update: null handle"); return DPK_E_BADARG; }
   if (!h->bound) { set_error("dpk_fused_update: buffers not bound"); return DPK_E_STATE; }
   if (adam_step < 1) { set_error("dpk_fused_update: adam_step %lld < 1", (long long)adam_step); return DPK_E_BADARG; }
   if (grad_mode < DPK_GRAD_KEEP || grad_mode > DPK_GRAD_ZERO) { set_error("dpk_fused_update: bad grad_mode"); return DPK_E_BADARG; }
+  int tb = 0, te = 0;
+  if (int rc = bucket_tiles(h, bucket, &tb, &te, "dpk_fused_update_bucket")) return rc;
   DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
 
@@ -590,11 +640,17 @@ int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam
     sc.rate[k] = (float)h->ema_rates[k];
     sc.alpha[k] = (float)(1.0 - h->ema_rates[k]);
   }
-  int rc = (h->dtype == DPK_F32)
-               ? launch_update<float>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, st)
-               : launch_update<__nv_bfloat16>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, st);
-  if (rc) return rc;
-  if ((rc = launch_segment_reduce(h, h->d_partials_post, st))) return rc;
+  return (h->dtype == DPK_F32)
+             ? launch_update<float>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, tb, te, st)
+             : launch_update<__nv_bfloat16>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, tb, te, st);
+}
+
+int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stream) {
+  if (!h) { set_error("dpk_fused_update_finish: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_fused_update: buffers not bound"); return DPK_E_STATE; }
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = launch_segment_reduce(h, h->d_partials_post, st)) return rc;
   if (h->dtype == DPK_F32)
     finalize_logged_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, skip_if_nonfinite, h->d_results);
   else
@@ -603,6 +659,14 @@ int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam
   h->launches++;
   DPK_CUDA(cudaGetLastError());
   return 0;
+}
+
+int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step, double inv_scale,
+                     int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode, void* stream) {
+  if (int rc = dpk_fused_update_bucket(h, -1, lr, weight_decay, adam_step, inv_scale, use_clip_coef,
+                                       skip_if_nonfinite, grad_mode, stream))
+    return rc;
+  return dpk_fused_update_finish(h, skip_if_nonfinite, stream);
 }
 
 int dpk_result_ptr(dpk_handle* h, void** d_out) {

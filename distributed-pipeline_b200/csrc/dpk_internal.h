@@ -93,6 +93,8 @@ struct dpk_handle {
   int world = 1, rank = 0;
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
+  std::vector<cudaEvent_t> ev_bucket_done;  // one per bucket
+  std::vector<char> bucket_pending;          // all-reduce enqueued, not yet waited for
   bool any_enqueued = false;
   std::mutex mu;
 

@@ -64,6 +64,13 @@ template <> struct ElemTraits<float> {
   }
   // value as stored in the state dtype
   static __device__ __forceinline__ float rnd(float x) { return x; }
+  // the same for a whole vector, in place
+  static __device__ __forceinline__ void rndv(float*) {}
+  // a 16-byte vector is processed in chunks of four elements
+  static constexpr int CH = 1;
+  static __device__ __forceinline__ void unpack4(const uint4& r, int, float* x) { unpack(r, x); }
+  static __device__ __forceinline__ void pack4(uint4& r, int, const float* x) { r = pack(x); }
+  static __device__ __forceinline__ void rnd4(float*) {}
 };
 template <> struct ElemTraits<__nv_bfloat16> {
   static constexpr int VE = 8;
@@ -79,14 +86,40 @@ template <> struct ElemTraits<__nv_bfloat16> {
     unsigned w[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      // inputs are already bf16-representable: truncation is exact
-      w[i] = (__float_as_uint(x[2 * i]) >> 16) | (__float_as_uint(x[2 * i + 1]) & 0xffff0000u);
+      // inputs are already bf16-representable: taking the high halves is exact (one PRMT)
+      w[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
     }
     return make_uint4(w[0], w[1], w[2], w[3]);
   }
   static __device__ __forceinline__ float rnd(float x) {
     return __bfloat162float(__float2bfloat16_rn(x));
   }
+  // Round-to-nearest-even to bf16, two lanes per instruction.  The scalar
+  // conversion compiles to F2F.BF16.F32, which issues on the quarter-rate XU
+  // pipe and made the bf16 kernels conversion-bound (ncu: XU 77%); the packed
+  // form is F2FP.BF16.F32.PACK_AB plus two integer ops.
+  static __device__ __forceinline__ void rnd2(float& a, float& b) {
+    unsigned w;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(b), "f"(a));
+    a = __uint_as_float(w << 16);
+    b = __uint_as_float(w & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void rndv(float* x) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) rnd2(x[2 * i], x[2 * i + 1]);
+  }
+  static constexpr int CH = 2;
+  static __device__ __forceinline__ void unpack4(const uint4& r, int c, float* x) {
+    const unsigned w0 = c ? r.z : r.x, w1 = c ? r.w : r.y;
+    x[0] = __uint_as_float(w0 << 16); x[1] = __uint_as_float(w0 & 0xffff0000u);
+    x[2] = __uint_as_float(w1 << 16); x[3] = __uint_as_float(w1 & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void pack4(uint4& r, int c, const float* x) {
+    const unsigned w0 = __byte_perm(__float_as_uint(x[0]), __float_as_uint(x[1]), 0x7632);
+    const unsigned w1 = __byte_perm(__float_as_uint(x[2]), __float_as_uint(x[3]), 0x7632);
+    if (c) { r.z = w0; r.w = w1; } else { r.x = w0; r.y = w1; }
+  }
+  static __device__ __forceinline__ void rnd4(float* x) { rnd2(x[0], x[1]); rnd2(x[2], x[3]); }
 };
 
 // streaming 128-bit accesses: every byte is touched once per pass
@@ -152,7 +185,7 @@ sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int 
     const uint4* gv = reinterpret_cast<const uint4*>(g + tile.start);
     const int nvec = (tile.len + VE - 1) / VE;
     float acc = 0.f;
-    unsigned bad = 0;
+    float nonfin = 0.f;
     for (int v0 = threadIdx.x; v0 < nvec; v0 += kThreads * U) {
       uint4 raw[U];
 #pragma unroll
@@ -166,16 +199,21 @@ sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int 
         float x[VE];
         Tr::unpack(raw[u], x);
         const int rem = tile.len - v * VE;  // valid lanes in this vector (<=0: none)
+        if (inv_scale != 1.0f) {  // x*1 is exact: the unscale and its store only exist with a loss scale
+#pragma unroll
+          for (int j = 0; j < VE; ++j) x[j] = __fmul_rn(x[j], inv_scale);
+          Tr::rndv(x);
+        }
 #pragma unroll
         for (int j = 0; j < VE; ++j) {
           if (j < rem) {
-            const float y = Tr::rnd(__fmul_rn(x[j], inv_scale));
-            bad |= nonfinite_bits(y) ? 1u : 0u;
-            acc = __fmaf_rn(y, y, acc);
+            nonfin = __fmaf_rn(x[j], 0.0f, nonfin);  // stays 0 unless x is inf/nan, then NaN for good
+            acc = __fmaf_rn(x[j], x[j], acc);
           }
         }
       }
     }
+    const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
     const int any_bad = __syncthreads_or((int)bad);
     const float s = block_sum(acc, red);
     if (threadIdx.x == 0) {
@@ -279,8 +317,8 @@ struct UpdateArgs {
   T* v;
   T* ema[K > 0 ? K : 1];
   const Tile* tiles;
-  int n_tiles;
-  TilePartial* partials;   // post-scale sum of squares per tile
+  int tile_begin, tile_end;  // this launch covers tiles [tile_begin, tile_end)
+  TilePartial* partials;     // post-scale sum of squares per tile
   const double* results;   // result block of the norm pass
   int use_clip_coef;
   int skip_if_nonfinite;
@@ -291,12 +329,12 @@ template <typename T, int K, int GM, bool FULL>
 __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long long vidx, int rem,
                                               float coef, float& acc) {
   using Tr = ElemTraits<T>;
-  constexpr int VE = Tr::VE;
   uint4* pv = reinterpret_cast<uint4*>(a.p) + vidx;
   uint4* gv = reinterpret_cast<uint4*>(a.g) + vidx;
   uint4* mv = reinterpret_cast<uint4*>(a.m) + vidx;
   uint4* vv = reinterpret_cast<uint4*>(a.v) + vidx;
 
+  // all loads of this vector are issued before any arithmetic
   const uint4 rg = (GM == DPK_GRAD_KEEP) ? ld_readonly(gv) : ld_stream(gv);
   const uint4 rp = ld_stream(pv);
   const uint4 rm = ld_stream(mv);
@@ -305,88 +343,121 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
 #pragma unroll
   for (int k = 0; k < K; ++k) re[k] = ld_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx);
 
-  float g[VE], p[VE], m[VE], v[VE];
-  Tr::unpack(rg, g);
-  Tr::unpack(rp, p);
-  Tr::unpack(rm, m);
-  Tr::unpack(rv, v);
+  // outputs start as the inputs so that lanes past a ragged end keep their bytes
+  uint4 wg = rg, wp = rp, wm = rm, wv = rv;
+  uint4 we[K > 0 ? K : 1];
+#pragma unroll
+  for (int k = 0; k < K; ++k) we[k] = re[k];
   const StepScalars& s = a.s;
 
 #pragma unroll
-  for (int j = 0; j < VE; ++j) {
-    // grad.mul_(1/2^lg) (upstream loss-scale), then _foreach_mul_(grads, coef)
-    float gj = Tr::rnd(__fmul_rn(g[j], s.inv_scale));
-    gj = Tr::rnd(__fmul_rn(gj, coef));
-    // (p.grad ** 2).sum(): the square is a tensor of the grad dtype
-    const float sq = Tr::rnd(__fmul_rn(gj, gj));
-    if (FULL || j < rem) acc = __fadd_rn(acc, sq);
+  for (int c = 0; c < Tr::CH; ++c) {
+    float g[4], p[4], m[4], v[4], t[4], d[4];
+    Tr::unpack4(rg, c, g);
+    Tr::unpack4(rp, c, p);
+    Tr::unpack4(rm, c, m);
+    Tr::unpack4(rv, c, v);
+    // Each block below is one torch kernel: compute in fp32, then the store to the
+    // state dtype (rnd4: nothing for fp32, round-to-nearest-even for bf16).
+    // grad.mul_(1/2^lg) (upstream loss-scale) and _foreach_mul_(grads, coef): a
+    // factor of exactly 1 changes no bit, so those two kernels are skipped then.
+    if (s.inv_scale != 1.0f) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[j] = __fmul_rn(g[j], s.inv_scale);
+      Tr::rnd4(g);
+    }
+    if (coef != 1.0f) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[j] = __fmul_rn(g[j], coef);
+      Tr::rnd4(g);
+    }
+    // (p.grad ** 2).sum(): the square is a tensor of the grad dtype; addcmul below
+    // squares again inside its own kernel, in fp32
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { t[j] = __fmul_rn(g[j], g[j]); d[j] = t[j]; }
+    Tr::rnd4(d);
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (FULL || c * 4 + j < rem) acc = __fadd_rn(acc, d[j]);
     // _foreach_mul_(params, 1 - lr*wd), skipped when wd == 0
-    float pj = s.has_decay ? Tr::rnd(__fmul_rn(p[j], s.decay)) : p[j];
+    if (s.has_decay) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) p[j] = __fmul_rn(p[j], s.decay);
+      Tr::rnd4(p);
+    }
     // _foreach_lerp_(exp_avg, grad, 1-beta1): m + w*(g-m), w < 0.5
-    const float mj = Tr::rnd(__fmaf_rn(s.w1, __fsub_rn(gj, m[j]), m[j]));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) m[j] = __fmaf_rn(s.w1, __fsub_rn(g[j], m[j]), m[j]);
+    Tr::rnd4(m);
     // _foreach_mul_(exp_avg_sq, beta2); _foreach_addcmul_(exp_avg_sq, g, g, 1-beta2)
-    float vj = Tr::rnd(__fmul_rn(v[j], s.beta2));
-    vj = Tr::rnd(__fmaf_rn(s.omb2, __fmul_rn(gj, gj), vj));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = __fmul_rn(v[j], s.beta2);
+    Tr::rnd4(v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = __fmaf_rn(s.omb2, t[j], v[j]);
+    Tr::rnd4(v);
     // _foreach_sqrt; _foreach_div_(bc2_sqrt); _foreach_add_(eps)
-    float d = Tr::rnd(__fsqrt_rn(vj));
-    d = Tr::rnd(__fdiv_rn(d, s.bc2_sqrt));
-    d = Tr::rnd(__fadd_rn(d, s.eps));
+#pragma unroll
+    for (int j = 0; j < 4; ++j) d[j] = __fsqrt_rn(v[j]);
+    Tr::rnd4(d);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) d[j] = __fdiv_rn(d[j], s.bc2_sqrt);
+    Tr::rnd4(d);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) d[j] = __fadd_rn(d[j], s.eps);
+    Tr::rnd4(d);
     // _foreach_addcdiv_(params, exp_avg, denom, -step_size)
-    pj = Tr::rnd(__fmaf_rn(s.neg_step, __fdiv_rn(mj, d), pj));
-    g[j] = gj;
-    p[j] = pj;
-    m[j] = mj;
-    v[j] = vj;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) p[j] = __fmaf_rn(s.neg_step, __fdiv_rn(m[j], d[j]), p[j]);
+    Tr::rnd4(p);
+
+    if (GM == DPK_GRAD_ZERO) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[j] = 0.f;
+    }
+    if (!FULL) {  // ragged last vector of a tensor
+      float og[4], op[4], om[4], ov[4];
+      Tr::unpack4(rg, c, og);
+      Tr::unpack4(rp, c, op);
+      Tr::unpack4(rm, c, om);
+      Tr::unpack4(rv, c, ov);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (c * 4 + j >= rem) { g[j] = og[j]; p[j] = op[j]; m[j] = om[j]; v[j] = ov[j]; }
+    }
+    Tr::pack4(wp, c, p);
+    Tr::pack4(wm, c, m);
+    Tr::pack4(wv, c, v);
+    if (GM != DPK_GRAD_KEEP) Tr::pack4(wg, c, g);
+
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      float e[4], oe[4];
+      Tr::unpack4(re[k], c, e);
+      // update_ema: trg.mul_(rate).add_(src, alpha=1-rate)  (utils/trainer.py:370),
+      // src being the parameters this step just produced
+#pragma unroll
+      for (int j = 0; j < 4; ++j) e[j] = __fmul_rn(e[j], s.rate[k]);
+      Tr::rnd4(e);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) e[j] = __fmaf_rn(s.alpha[k], p[j], e[j]);
+      Tr::rnd4(e);
+      if (!FULL) {
+        Tr::unpack4(re[k], c, oe);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (c * 4 + j >= rem) e[j] = oe[j];
+      }
+      Tr::pack4(we[k], c, e);
+    }
   }
 
-  if (FULL) {
-    st_stream(pv, Tr::pack(p));
-    st_stream(mv, Tr::pack(m));
-    st_stream(vv, Tr::pack(v));
-    if (GM == DPK_GRAD_CLIPPED) st_stream(gv, Tr::pack(g));
-    if (GM == DPK_GRAD_ZERO) st_stream(gv, make_uint4(0, 0, 0, 0));
+  st_stream(pv, wp);
+  st_stream(mv, wm);
+  st_stream(vv, wv);
+  if (GM != DPK_GRAD_KEEP) st_stream(gv, wg);
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-      float e[VE];
-      Tr::unpack(re[k], e);
-#pragma unroll
-      for (int j = 0; j < VE; ++j) {
-        // update_ema: trg.mul_(rate).add_(src, alpha=1-rate)  (utils/trainer.py:370)
-        const float t = Tr::rnd(__fmul_rn(e[j], s.rate[k]));
-        e[j] = Tr::rnd(__fmaf_rn(s.alpha[k], p[j], t));
-      }
-      st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, Tr::pack(e));
-    }
-  } else {
-    // ragged last vector of a tensor: lanes past the end keep their bytes
-    float op[VE], om[VE], ov[VE], og[VE];
-    Tr::unpack(rp, op);
-    Tr::unpack(rm, om);
-    Tr::unpack(rv, ov);
-    Tr::unpack(rg, og);
-#pragma unroll
-    for (int j = 0; j < VE; ++j) {
-      if (j >= rem) { p[j] = op[j]; m[j] = om[j]; v[j] = ov[j]; g[j] = og[j]; }
-      else if (GM == DPK_GRAD_ZERO) g[j] = 0.f;
-    }
-    st_stream(pv, Tr::pack(p));
-    st_stream(mv, Tr::pack(m));
-    st_stream(vv, Tr::pack(v));
-    if (GM != DPK_GRAD_KEEP) st_stream(gv, Tr::pack(g));
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      float e[VE];
-      Tr::unpack(re[k], e);
-#pragma unroll
-      for (int j = 0; j < VE; ++j) {
-        if (j < rem) {
-          const float t = Tr::rnd(__fmul_rn(e[j], s.rate[k]));
-          e[j] = Tr::rnd(__fmaf_rn(s.alpha[k], p[j], t));
-        }
-      }
-      st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, Tr::pack(e));
-    }
-  }
+  for (int k = 0; k < K; ++k) st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, we[k]);
 }
 
 template <typename T, int K, int GM, int U>
@@ -398,7 +469,7 @@ fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
   if (a.skip_if_nonfinite && a.results[DPK_R_NONFINITE] != 0.0) return;
   const float coef = a.use_clip_coef ? (float)a.results[DPK_R_CLIP_COEF] : 1.0f;
 
-  for (int t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+  for (int t = a.tile_begin + blockIdx.x; t < a.tile_end; t += gridDim.x) {
     const Tile tile = a.tiles[t];
     const long long vbase = tile.start / VE;
     const int nfull = tile.len / VE;  // vectors with every lane valid

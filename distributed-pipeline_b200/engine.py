@@ -123,6 +123,9 @@ class Engine:
     def bucket_ready(self, b: int, stream=None):
         _lib.check(self.lib.dpk_bucket_ready(self._h, b, _stream_ptr(stream, self.device)))
 
+    def wait_bucket(self, b: int, stream=None):
+        _lib.check(self.lib.dpk_wait_bucket(self._h, b, _stream_ptr(stream, self.device)))
+
     def wait_allreduce(self, stream=None):
         _lib.check(self.lib.dpk_wait_allreduce(self._h, _stream_ptr(stream, self.device)))
 
@@ -141,6 +144,24 @@ class Engine:
                      grad_mode: int = _lib.GRAD_KEEP, stream=None):
         _lib.check(self.lib.dpk_fused_update(self._h, lr, weight_decay, adam_step, inv_scale, int(use_clip_coef),
                                              int(skip_if_nonfinite), grad_mode, _stream_ptr(stream, self.device)))
+
+    # -- the same two passes, one all-reduce bucket at a time ---------------------
+    def grad_norm_bucket(self, bucket: int, inv_scale: float = 1.0, stream=None):
+        _lib.check(self.lib.dpk_grad_norm_bucket(self._h, bucket, inv_scale, _stream_ptr(stream, self.device)))
+
+    def grad_norm_finish(self, max_norm: float = 0.0, stream=None):
+        _lib.check(self.lib.dpk_grad_norm_finish(self._h, max_norm, _stream_ptr(stream, self.device)))
+
+    def fused_update_bucket(self, bucket: int, lr: float, weight_decay: float, adam_step: int,
+                            inv_scale: float = 1.0, use_clip_coef: bool = False, skip_if_nonfinite: bool = False,
+                            grad_mode: int = _lib.GRAD_KEEP, stream=None):
+        _lib.check(self.lib.dpk_fused_update_bucket(self._h, bucket, lr, weight_decay, adam_step, inv_scale,
+                                                    int(use_clip_coef), int(skip_if_nonfinite), grad_mode,
+                                                    _stream_ptr(stream, self.device)))
+
+    def fused_update_finish(self, skip_if_nonfinite: bool = False, stream=None):
+        _lib.check(self.lib.dpk_fused_update_finish(self._h, int(skip_if_nonfinite),
+                                                    _stream_ptr(stream, self.device)))
 
     @property
     def results(self) -> torch.Tensor:

@@ -66,6 +66,36 @@ class FusedAdamW:
         self._clip_pending = False
         self.ema_done = [True] * len(self.ema_rates)
 
+    @torch.no_grad()
+    def reduce_and_step(self, max_norm: float = -1.0):
+        """The whole post-backward update when every local gradient is already in
+        the flat buffer: enqueue the all-reduce of every bucket, then consume
+        buckets as they land -- bucket b is updated (or, when clipping, summed
+        into the norm) while bucket b+1 is still on NVLink.  Same results as
+        all-reduce -> clip_grad_norm -> step."""
+        eng = self.engine
+        g = self.param_groups[0]
+        n = len(eng.buckets)
+        if eng.world_size > 1:
+            for b in range(n):
+                eng.bucket_ready(b)
+        if max_norm > 0:
+            for b in range(n):
+                eng.wait_bucket(b)
+                eng.grad_norm_bucket(b, self.inv_scale)
+            eng.grad_norm_finish(float(max_norm))
+            self._clip_pending = True
+            return self.step()
+        self.step_count += 1
+        for b in range(n):
+            eng.wait_bucket(b)
+            eng.fused_update_bucket(b, float(g["lr"]), float(g["weight_decay"]), self.step_count,
+                                    inv_scale=self.inv_scale, use_clip_coef=False,
+                                    skip_if_nonfinite=False, grad_mode=self.grad_mode)
+        eng.fused_update_finish(False)
+        self._clip_pending = False
+        self.ema_done = [True] * len(self.ema_rates)
+
     def undo_step_count(self):
         """A predicated-off (non-finite) step must not advance AdamW's step."""
         self.step_count -= 1

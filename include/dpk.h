@@ -123,6 +123,10 @@ int dpk_bucket_range(const dpk_handle* h, int32_t b, int64_t* start, int64_t* co
  * its all-reduce on the library's communication stream.  Thread-safe (it is
  * called from autograd's engine thread). */
 int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream);
+/* Make `consumer_stream` wait for bucket b's all-reduce only (no-op if none is
+ * outstanding): lets the caller consume buckets as they land while later ones
+ * are still on the wire. */
+int dpk_wait_bucket(dpk_handle* h, int32_t b, void* consumer_stream);
 /* Make `consumer_stream` wait for every all-reduce enqueued so far. */
 int dpk_wait_allreduce(dpk_handle* h, void* consumer_stream);
 /* One coalesced broadcast of params (+ every EMA copy if include_ema) from
@@ -157,6 +161,21 @@ int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream
 int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
                      double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite,
                      int32_t grad_mode, void* stream);
+
+/* The two passes cut along the all-reduce buckets, so that a bucket can be
+ * consumed the moment its all-reduce lands while the next one is still in
+ * flight (torch DDP overlaps its reducer with backward in the same spirit,
+ * utils/trainer.py:118-125; here the update itself overlaps the reducer):
+ *   dpk_grad_norm    == dpk_grad_norm_bucket(-1)  + dpk_grad_norm_finish
+ *   dpk_fused_update == dpk_fused_update_bucket(-1) + dpk_fused_update_finish
+ * bucket = -1 means the whole buffer.  Every bucket must be processed exactly
+ * once before the matching _finish; results are identical to the one-call forms. */
+int dpk_grad_norm_bucket(dpk_handle* h, int32_t bucket, double inv_scale, void* stream);
+int dpk_grad_norm_finish(dpk_handle* h, double max_norm, void* stream);
+int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double weight_decay,
+                            int64_t adam_step, double inv_scale, int32_t use_clip_coef,
+                            int32_t skip_if_nonfinite, int32_t grad_mode, void* stream);
+int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stream);
 
 /* Device address of the result block (DPK_R_COUNT doubles). */
 int dpk_result_ptr(dpk_handle* h, void** d_out);

@@ -88,6 +88,36 @@ def test_norm_matches_oracle_and_segments(dtype):
         assert c.to(torch.bfloat16).double() == c  # coefficient is bf16-representable
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_bucket_granular_passes_equal_whole_buffer_passes(dtype):
+    """dpk_*_bucket over every bucket + _finish == the one-call forms, bit for bit."""
+    numels = [5000, 3, 70000, 128, 9000, 33, 40000]
+    a = FlatProblem(numels, dtype, [0.999, 0.9], seed=9, bucket_cap_bytes=64 * 1024)
+    b = FlatProblem(numels, dtype, [0.999, 0.9], seed=9, bucket_cap_bytes=64 * 1024, mirror=False)
+    n_buckets = len(a.engine.buckets)
+    assert n_buckets >= 3
+    for step in (1, 2):
+        g = a.new_grads(std=0.3)
+        b.g.copy_(a.g)
+        a.engine.grad_norm(1.0, 1.0)
+        a.engine.fused_update(1e-3, 0.01, step, use_clip_coef=True, grad_mode=_lib.GRAD_CLIPPED)
+        for k in reversed(range(n_buckets)):           # any order
+            b.engine.wait_bucket(k)                    # no all-reduce outstanding: no-op
+            b.engine.grad_norm_bucket(k, 1.0)
+        b.engine.grad_norm_finish(1.0)
+        for k in range(n_buckets):
+            b.engine.fused_update_bucket(k, 1e-3, 0.01, step, use_clip_coef=True, grad_mode=_lib.GRAD_CLIPPED)
+        b.engine.fused_update_finish()
+        ra, rb = a.engine.read_results_sync(), b.engine.read_results_sync()
+        assert ra == rb
+        for x, y, name in zip((a.p, a.m, a.v, a.g, *a.emas), (b.p, b.m, b.v, b.g, *b.emas), "pmvgee"):
+            m = a.mask.to(x.device)
+            assert torch.equal(x[m], y[m]), name
+    from distributed_pipeline_b200 import DpkError
+    with pytest.raises(DpkError):
+        b.engine.fused_update_bucket(n_buckets, 1e-3, 0.0, 1)
+
+
 def test_clip_inactive_gives_unit_coef():
     pb = FlatProblem([1000, 50], torch.float32, [0.99], seed=5)
     g = pb.new_grads(std=1e-4)
