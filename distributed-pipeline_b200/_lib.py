@@ -84,6 +84,7 @@ SIGNATURES = {
     "dpk_timing_enable": (C.c_int, [_VP, C.c_int32]),
     "dpk_timing_read_sync": (C.c_int, [_VP, C.c_int32, C.POINTER(C.c_float), C.c_int32, C.POINTER(C.c_int32)]),
     "dpk_launch_count": (C.c_int, [_VP, C.POINTER(C.c_int64)]),
+    "dpk_selftest_arith": (C.c_int, [C.c_double, _VP, _VP]),
     "dpk_ema_update": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_double, _VP]),
     "dpk_sampler_create": (C.c_int, [C.POINTER(_VP), C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_int32]),
     "dpk_sampler_destroy": (C.c_int, [_VP]),

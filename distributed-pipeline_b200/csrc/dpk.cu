@@ -151,11 +151,11 @@ static int launch_sumsq(dpk_handle* h, int tile_begin, int tile_end, float inv_s
   return 0;
 }
 
-static int launch_segment_reduce(dpk_handle* h, const TilePartial* partials, cudaStream_t st) {
+static int launch_segment_reduce(dpk_handle* h, const TilePartial* partials, int per_tile, cudaStream_t st) {
   if (h->n_seg == 0) return 0;
   const int grid = std::min(h->n_seg, 4 * h->sm_count);
   segment_reduce_kernel<<<grid, kThreads, 0, st>>>(partials, h->d_seg_tile_begin, h->d_seg_sumsq,
-                                                   h->d_seg_bad, h->n_seg);
+                                                   h->d_seg_bad, h->n_seg, per_tile);
   h->launches++;
   DPK_CUDA(cudaGetLastError());
   return 0;
@@ -174,15 +174,17 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   a.tiles = h->d_tiles;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
+  a.chunk_elems = h->chunk_elems;
+  a.chunks_per_tile = h->chunks_per_tile;
   a.partials = h->d_partials_post;
   a.results = h->d_results;
   a.use_clip_coef = use_coef;
   a.skip_if_nonfinite = skip;
   a.s = sc;
-  // vectors in flight per thread and array: 2 x 4 fp32 elements, 1 x 8 bf16 elements
-  auto kern = fused_update_kernel<T, K, GM, (sizeof(T) == 4 ? 2 : 1)>;
+  auto kern = fused_update_kernel<T, K, GM>;
   int grid = 0;
-  if (int rc = grid_for(kern, n_tiles, h->sm_count, &grid)) return rc;
+  const long long items = (long long)n_tiles * h->chunks_per_tile;
+  if (int rc = grid_for(kern, (int)std::min<long long>(items, 1 << 30), h->sm_count, &grid)) return rc;
   {
     KernelTimer timer(h, 0, st);
     kern<<<grid, kThreads, 0, st>>>(a);
@@ -250,7 +252,7 @@ static int ensure_device_state(dpk_handle* h) {
   DPK_CUDA(cudaMalloc(&h->d_tiles, nt * sizeof(Tile)));
   DPK_CUDA(cudaMalloc(&h->d_seg_tile_begin, (ns + 1) * sizeof(int)));
   DPK_CUDA(cudaMalloc(&h->d_partials_pre, nt * sizeof(TilePartial)));
-  DPK_CUDA(cudaMalloc(&h->d_partials_post, nt * sizeof(TilePartial)));
+  DPK_CUDA(cudaMalloc(&h->d_partials_post, nt * h->chunks_per_tile * sizeof(TilePartial)));
   DPK_CUDA(cudaMalloc(&h->d_seg_sumsq, ns * sizeof(double)));
   DPK_CUDA(cudaMalloc(&h->d_seg_bad, ns * sizeof(unsigned)));
   DPK_CUDA(cudaMalloc(&h->d_seg_norms, ns * sizeof(double)));
@@ -328,6 +330,10 @@ int dpk_create(dpk_handle** out, const dpk_config* cfg) {
   h->n_seg = cfg->n_segments;
   h->n_ema = cfg->n_ema;
   h->tile_elems = tile_elems;
+  // pass 2 deals out chunks of one vector per thread; fall back to 1024 elements
+  // when the tile size is not a multiple of that
+  h->chunk_elems = (tile_elems % (kThreads * ve) == 0) ? kThreads * ve : 1024;
+  h->chunks_per_tile = tile_elems / h->chunk_elems;
   h->n_elems = cfg->n_elems;
   h->beta1 = cfg->beta1; h->beta2 = cfg->beta2; h->eps = cfg->eps;
   for (int k = 0; k < cfg->n_ema; ++k) h->ema_rates[k] = cfg->ema_rates[k];
@@ -591,7 +597,7 @@ int dpk_grad_norm_finish(dpk_handle* h, double max_norm, void* stream) {
   if (!h->bound) { set_error("dpk_grad_norm: buffers not bound"); return DPK_E_STATE; }
   DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
-  if (int rc = launch_segment_reduce(h, h->d_partials_pre, st)) return rc;
+  if (int rc = launch_segment_reduce(h, h->d_partials_pre, 1, st)) return rc;
   if (h->dtype == DPK_F32)
     finalize_norm_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->d_seg_bad, h->n_seg, (float)max_norm,
                                                         h->d_seg_norms, h->d_results);
@@ -634,6 +640,7 @@ int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double wei
   sc.beta2 = (float)h->beta2;
   sc.omb2 = (float)(1.0 - h->beta2);
   sc.bc2_sqrt = (float)pow(bc2, 0.5);
+  sc.bc2_rcp = (float)(1.0 / (double)sc.bc2_sqrt);  // correctly rounded reciprocal of the fp32 divisor
   sc.eps = (float)h->eps;
   sc.neg_step = (float)((lr / bc1) * -1.0);
   for (int k = 0; k < h->n_ema; ++k) {
@@ -650,7 +657,7 @@ int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stre
   if (!h->bound) { set_error("dpk_fused_update: buffers not bound"); return DPK_E_STATE; }
   DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
-  if (int rc = launch_segment_reduce(h, h->d_partials_post, st)) return rc;
+  if (int rc = launch_segment_reduce(h, h->d_partials_post, h->chunks_per_tile, st)) return rc;
   if (h->dtype == DPK_F32)
     finalize_logged_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, skip_if_nonfinite, h->d_results);
   else

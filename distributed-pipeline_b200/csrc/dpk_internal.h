@@ -63,6 +63,8 @@ struct dpk_handle {
   int n_seg = 0;
   int n_ema = 0;
   int tile_elems = 0;
+  int chunk_elems = 0;      // pass-2 work item; divides tile_elems
+  int chunks_per_tile = 1;
   long long n_elems = 0;
   double beta1 = 0.9, beta2 = 0.999, eps = 1e-8;
   double ema_rates[DPK_MAX_EMA] = {0};

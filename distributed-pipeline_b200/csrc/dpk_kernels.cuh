@@ -43,6 +43,7 @@ struct StepScalars {
   float beta2;
   float omb2;        // 1 - beta2
   float bc2_sqrt;    // sqrt(1 - beta2^t)
+  float bc2_rcp;     // fp32(1 / bc2_sqrt), for the exact scalar division below
   float eps;
   float neg_step;    // -(lr / (1 - beta1^t))
   float rate[DPK_MAX_EMA];
@@ -50,6 +51,27 @@ struct StepScalars {
 };
 
 // ---------------------------------------------------------------- helpers --
+
+// x / c for a divisor that is the same for every element, correctly rounded
+// (identical to div.rn.f32) at a third of its cost: with rc = RN(1/c),
+// q = RN(x*rc), r = x - q*c (exact in one FMA), RN(q + r*rc) is the correctly
+// rounded quotient (Markstein) as long as neither it nor the remainder is
+// subnormal -- true here, where x is a freshly stored square root (0 or at
+// least 2^-75) and c lies in [0.03, 1].  inf/NaN fall through unchanged.
+// dpk_selftest_arith checks it against div.rn for the square root of every
+// fp32 bit pattern.
+__device__ __forceinline__ float div_by_scalar(float x, float c, float rc) {
+  const float q = __fmul_rn(x, rc);
+  const float r = __fmaf_rn(-q, c, x);
+  const float q1 = __fmaf_rn(r, rc, q);
+  return (fabsf(q) < __int_as_float(0x7f800000)) ? q1 : q;
+}
+
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 
 template <typename T> struct ElemTraits;
 template <> struct ElemTraits<float> {
@@ -67,6 +89,8 @@ template <> struct ElemTraits<float> {
   // the same for a whole vector, in place
   static __device__ __forceinline__ void rndv(float*) {}
   // a 16-byte vector is processed in chunks of four elements
+  // sqrt whose result is about to be stored in the state dtype
+  static __device__ __forceinline__ float sqrt_for_store(float x) { return __fsqrt_rn(x); }
   static constexpr int CH = 1;
   static __device__ __forceinline__ void unpack4(const uint4& r, int, float* x) { unpack(r, x); }
   static __device__ __forceinline__ void pack4(uint4& r, int, const float* x) { r = pack(x); }
@@ -108,6 +132,10 @@ template <> struct ElemTraits<__nv_bfloat16> {
 #pragma unroll
     for (int i = 0; i < 4; ++i) rnd2(x[2 * i], x[2 * i + 1]);
   }
+  // The square root of a bf16 value is never closer than 2^-18 (relative) to the
+  // midpoint of two bf16 values (all 32 639 positive inputs enumerated), so the
+  // 2^-23-accurate sqrt.approx rounds to the same bf16 as the IEEE one.
+  static __device__ __forceinline__ float sqrt_for_store(float x) { return sqrt_approx(x); }
   static constexpr int CH = 2;
   static __device__ __forceinline__ void unpack4(const uint4& r, int c, float* x) {
     const unsigned w0 = c ? r.z : r.x, w1 = c ? r.w : r.y;
@@ -225,17 +253,20 @@ sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int 
   }
 }
 
-// Second level: one block per tensor sums that tensor's tile partials in fp64.
+// Second level: one block per tensor sums that tensor's partials in fp64.
+// `per_tile` partials were written for every tile (1 by pass 1, chunks-per-tile
+// by pass 2), laid out tile-major.
 static __global__ void __launch_bounds__(kThreads)
 segment_reduce_kernel(const TilePartial* __restrict__ partials,
                       const int* __restrict__ seg_tile_begin /*[n_seg+1]*/,
-                      double* __restrict__ seg_sumsq, unsigned* __restrict__ seg_bad, int n_seg) {
+                      double* __restrict__ seg_sumsq, unsigned* __restrict__ seg_bad, int n_seg,
+                      int per_tile) {
   __shared__ double red[kThreads / 32];
   for (int s = blockIdx.x; s < n_seg; s += gridDim.x) {
-    const int b = seg_tile_begin[s], e = seg_tile_begin[s + 1];
+    const long long b = (long long)seg_tile_begin[s] * per_tile, e = (long long)seg_tile_begin[s + 1] * per_tile;
     double acc = 0.0;
     unsigned bad = 0;
-    for (int t = b + threadIdx.x; t < e; t += kThreads) {
+    for (long long t = b + threadIdx.x; t < e; t += kThreads) {
       const TilePartial p = partials[t];
       acc += (double)p.sumsq;
       bad |= p.bad;
@@ -318,7 +349,9 @@ struct UpdateArgs {
   T* ema[K > 0 ? K : 1];
   const Tile* tiles;
   int tile_begin, tile_end;  // this launch covers tiles [tile_begin, tile_end)
-  TilePartial* partials;     // post-scale sum of squares per tile
+  int chunk_elems;           // elements per work item: one 16-byte vector per thread
+  int chunks_per_tile;       // tile_elems / chunk_elems
+  TilePartial* partials;     // sum of squares per (tile, chunk), tile-major
   const double* results;   // result block of the norm pass
   int use_clip_coef;
   int skip_if_nonfinite;
@@ -398,10 +431,10 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
     Tr::rnd4(v);
     // _foreach_sqrt; _foreach_div_(bc2_sqrt); _foreach_add_(eps)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) d[j] = __fsqrt_rn(v[j]);
+    for (int j = 0; j < 4; ++j) d[j] = Tr::sqrt_for_store(v[j]);
     Tr::rnd4(d);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) d[j] = __fdiv_rn(d[j], s.bc2_sqrt);
+    for (int j = 0; j < 4; ++j) d[j] = div_by_scalar(d[j], s.bc2_sqrt, s.bc2_rcp);
     Tr::rnd4(d);
 #pragma unroll
     for (int j = 0; j < 4; ++j) d[j] = __fadd_rn(d[j], s.eps);
@@ -460,37 +493,74 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
   for (int k = 0; k < K; ++k) st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, we[k]);
 }
 
-template <typename T, int K, int GM, int U>
-__global__ void __launch_bounds__(kThreads)
+// Work distribution.  A work item is one *chunk*: kThreads consecutive 16-byte
+// vectors (4 KiB) of every array, one vector per thread.  Items are dealt to the
+// resident blocks round-robin, so at any moment the whole grid streams through
+// one compact window of each array -- measured on B200 this is worth 6 % of HBM
+// bandwidth over letting each block walk a private 32 KiB tile (DRAM pages stay
+// open).  Chunks never straddle a tile, hence never a tensor; the tile
+// descriptor of the next item is fetched while the current one is processed.
+// resident blocks per SM the register allocation is asked to allow
+template <typename T, int K>
+constexpr int update_min_blocks() { return sizeof(T) == 4 ? (K <= 2 ? 4 : 3) : (K <= 2 ? 3 : 2); }
+
+template <typename T, int K, int GM>
+__global__ void __launch_bounds__(kThreads, update_min_blocks<T, K>())
 fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
   using Tr = ElemTraits<T>;
   constexpr int VE = Tr::VE;
-  __shared__ float red[kThreads / 32];
+  __shared__ float red[2][kThreads / 32];
   if (a.skip_if_nonfinite && a.results[DPK_R_NONFINITE] != 0.0) return;
   const float coef = a.use_clip_coef ? (float)a.results[DPK_R_CLIP_COEF] : 1.0f;
+  // item = tile * chunks_per_tile + chunk, advanced by gridDim.x per iteration
+  // without a division in the loop
+  const int cpt = a.chunks_per_tile;
+  const int step_tiles = gridDim.x / cpt, step_chunks = gridDim.x % cpt;
+  int tix = a.tile_begin + blockIdx.x / cpt;
+  int chunk = blockIdx.x % cpt;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-  for (int t = a.tile_begin + blockIdx.x; t < a.tile_end; t += gridDim.x) {
-    const Tile tile = a.tiles[t];
-    const long long vbase = tile.start / VE;
-    const int nfull = tile.len / VE;  // vectors with every lane valid
-    const int nvec = (tile.len + VE - 1) / VE;
+  Tile next;
+  next.start = 0; next.len = 0; next.seg = 0;
+  if (tix < a.tile_end) next = a.tiles[tix];
+  int buf = 0;
+  while (tix < a.tile_end) {
+    const Tile tile = next;
+    const int cur_tile = tix, cur_chunk = chunk;
+    chunk += step_chunks;
+    tix += step_tiles;
+    if (chunk >= cpt) { chunk -= cpt; ++tix; }
+    if (tix < a.tile_end) next = a.tiles[tix];
+
+    const int off = cur_chunk * a.chunk_elems;
+    int len = tile.len - off;                       // elements of this chunk (<= 0: past a short tile's end)
+    len = len > a.chunk_elems ? a.chunk_elems : len;
+    const long long vbase = (tile.start + off) / VE;
+    const int nfull = len > 0 ? len / VE : 0;       // vectors with every lane valid
     float acc = 0.f;
-    for (int v0 = threadIdx.x; v0 < nfull; v0 += kThreads * U) {
+    const int v = threadIdx.x;
+    if (v < nfull)
+      update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
+    else if (v == nfull && len > nfull * VE)        // ragged end of a tensor: one masked vector
+      update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc);
+
+    // block sum, fixed order, one barrier per item (the exchange buffer alternates)
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * kThreads;
-        if (v < nfull) update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
+    for (int o = 16; o > 0; o >>= 1) acc = __fadd_rn(acc, __shfl_down_sync(0xffffffffu, acc, o));
+    if (lane == 0) red[buf][warp] = acc;
+    __syncthreads();
+    if (warp == 0) {
+      float r = (lane < kThreads / 32) ? red[buf][lane] : 0.f;
+#pragma unroll
+      for (int o = 4; o > 0; o >>= 1) r = __fadd_rn(r, __shfl_down_sync(0xffffffffu, r, o));
+      if (lane == 0) {
+        TilePartial p;
+        p.sumsq = r;
+        p.bad = 0;
+        a.partials[(long long)cur_tile * cpt + cur_chunk] = p;
       }
     }
-    if (nvec != nfull && threadIdx.x == 0)
-      update_vector<T, K, GM, false>(a, vbase + nfull, tile.len - nfull * VE, coef, acc);
-    const float s = block_sum(acc, red);
-    if (threadIdx.x == 0) {
-      TilePartial p;
-      p.sumsq = s;
-      p.bad = 0;
-      a.partials[t] = p;
-    }
+    buf ^= 1;
   }
 }
 

@@ -140,7 +140,7 @@ static int run_static(const void* d_g, long long n, int n_tiles, float inv_scale
   if (grid < 1) grid = 1;
   sumsq_flat_kernel<T, 4><<<(int)grid, kThreads, 0, st>>>((const T*)d_g, n, n_tiles, inv_scale, sc);
   DPK_CUDA(cudaGetLastError());
-  segment_reduce_kernel<<<1, kThreads, 0, st>>>(sc->partials, sc->seg_tile_begin, sc->seg_sumsq, sc->seg_bad, 1);
+  segment_reduce_kernel<<<1, kThreads, 0, st>>>(sc->partials, sc->seg_tile_begin, sc->seg_sumsq, sc->seg_bad, 1, 1);
   DPK_CUDA(cudaGetLastError());
   finalize_norm_kernel<T><<<1, kThreads, 0, st>>>(sc->seg_sumsq, sc->seg_bad, 1, max_norm, sc->seg_norms, d_out);
   DPK_CUDA(cudaGetLastError());

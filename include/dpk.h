@@ -234,6 +234,14 @@ int dpk_timing_enable(dpk_handle* h, int32_t on);
 int dpk_timing_read_sync(dpk_handle* h, int32_t which, float* ms_out, int32_t cap, int32_t* n_out);
 /* Kernels this handle has launched since creation. */
 int dpk_launch_count(const dpk_handle* h, int64_t* out);
+/* Exhaustive device-side check of the fused kernel's two arithmetic shortcuts
+ * against the IEEE operations they stand in for: d_out2[0] = number of fp32 bit
+ * patterns v (all 2^32) for which the reciprocal-and-correct division of
+ * sqrt(v) -- the only dividends the kernel has -- by `divisor` differs from
+ * div.rn; d_out2[1] = number of bf16 bit patterns whose
+ * approximate square root rounds to a different bf16 than sqrt.rn's.  Both must
+ * be 0.  d_out2: two device uint64. */
+int dpk_selftest_arith(double divisor, unsigned long long* d_out2, void* stream);
 
 /* ---- loss-aware timestep sampler.  Absent from the reference;
  * semantics are upstream improved-diffusion resample.py

@@ -207,3 +207,24 @@ def test_error_paths():
         Engine(pb.layout, torch.float32, "cuda:0", [0.1] * 5)
     with pytest.raises(RuntimeError):
         Engine(pb.layout, torch.float32, "cpu", [])
+
+
+def test_arithmetic_shortcuts_are_exact_for_every_input():
+    """The fused kernel divides by the per-step scalar sqrt(1-beta2^t) with a
+    reciprocal + two FMAs and, for bf16 state, takes sqrt.approx before rounding
+    to bf16.  Both must be indistinguishable from div.rn / sqrt.rn: checked on
+    the device for the square root of every fp32 bit pattern (the only dividends
+    the kernel has), per divisor, and for all 2^16 bf16 inputs."""
+    lib = _lib.lib()
+    out = torch.zeros(2, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    steps = [1, 2, 3, 10, 100, 1000, 5000, 100000]
+    for t in steps:
+        c = (1 - 0.999 ** t) ** 0.5
+        _lib.check(lib.dpk_selftest_arith(c, out.data_ptr(), stream))
+        bad_div, bad_sqrt = out.cpu().tolist()
+        assert bad_div == 0, f"scalar division differs from div.rn for {bad_div} inputs at step {t} (c={c})"
+        assert bad_sqrt == 0
+    for c in (0.3, 1.0, 0.7071067811865476, 0.0316, 0.999):
+        _lib.check(lib.dpk_selftest_arith(c, out.data_ptr(), stream))
+        assert out.cpu().tolist() == [0, 0], c
