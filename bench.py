@@ -49,8 +49,10 @@ def parse_args():
                     help="sweep mode: one flat tensor of this many parameters instead of the model shapes")
     ap.add_argument("--grad-mode", default="keep", choices=["keep", "clipped", "zero"])
     ap.add_argument("--tile-elems", type=int, default=0)
-    ap.add_argument("--bucket-mb", type=float, default=32.0,
+    ap.add_argument("--bucket-mb", type=float, default=128.0,
                     help="all-reduce bucket size for N>1 (reference DDP: 128; results do not depend on it)")
+    ap.add_argument("--allreduce", choices=["nvls", "nccl"], default="nvls",
+                    help="N>1: the library's own NVLS (multimem) all-reduce kernel, or ncclAllReduce")
     ap.add_argument("--no-overlap", action="store_true",
                     help="N>1: finish the whole all-reduce before the update instead of consuming buckets as they land")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -239,12 +241,15 @@ def run_ours(args):
     gen = torch.Generator(device=dev).manual_seed(102)  # params identical on every rank
     params = [torch.nn.Parameter((torch.randn(s, generator=gen, device=dev) * 0.02).to(tdt)) for s in shapes]
     opt = FusedAdamW(params, lr=LR, weight_decay=wd, ema_rates=rates, grad_mode=gm, tile_elems=args.tile_elems,
-                     bucket_cap_mb=args.bucket_mb if world > 1 else 128)
+                     bucket_cap_mb=args.bucket_mb if world > 1 else 128,
+                     symmetric_grads=world > 1 and args.allreduce == "nvls")
     del params
     eng, flat = opt.engine, opt.flat
     if world > 1:
         eng.init_comm()
         eng.broadcast_state(0, True)
+        if args.allreduce == "nvls":
+            eng.enable_nvls(flat.grads)
     ggen = torch.Generator(device=dev).manual_seed(4321 + rank)
     sigma = 1e-3
     grads_src = (torch.randn(flat.layout.n_elems, generator=ggen, device=dev) * sigma).to(tdt)
@@ -381,6 +386,7 @@ def run_ours(args):
                        "l2_policy": f"inputs larger than L2 ({n_params * bpp / 1e6:.0f} MB streamed per step vs 126 MB L2)",
                        "allreduce_buckets": n_buckets if world > 1 else 0,
                        "bucket_mb": args.bucket_mb if world > 1 else None,
+                       "allreduce": (args.allreduce if world > 1 else None),
                        "update_overlaps_allreduce": bool(world > 1 and not args.no_overlap),
                        "grad_sigma": sigma},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,

@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdpk.so")
-SOURCES = ["dpk.cu", "dpk_sampler.cu", "dpk_noalloc.cu", "dpk_selftest.cu"]
+SOURCES = ["dpk.cu", "dpk_sampler.cu", "dpk_noalloc.cu", "dpk_selftest.cu", "dpk_nvls.cu"]
 HEADERS = ["dpk_kernels.cuh", "dpk_internal.h", os.path.join("..", "..", "include", "dpk.h")]
 
 

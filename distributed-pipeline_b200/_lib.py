@@ -62,6 +62,7 @@ SIGNATURES = {
     "dpk_comm_unique_id": (C.c_int, [_VP]),
     "dpk_comm_init": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32]),
     "dpk_world_size": (C.c_int, [_VP]),
+    "dpk_bind_nvls": (C.c_int, [_VP, _VP, C.POINTER(_VP), _VP, _VP, C.c_int32]),
     "dpk_num_buckets": (C.c_int, [_VP]),
     "dpk_bucket_range": (C.c_int, [_VP, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "dpk_bucket_ready": (C.c_int, [_VP, C.c_int32, _VP]),

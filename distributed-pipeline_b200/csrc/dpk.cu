@@ -168,6 +168,7 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
                               int tile_end, cudaStream_t st) {
   const int n_tiles = tile_end - tile_begin;
   if (n_tiles <= 0) return 0;
+  const bool whole_buffer = tile_begin == 0 && tile_end == (int)h->tiles.size();
   UpdateArgs<T, K> a;
   a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
   for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
@@ -185,9 +186,14 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   int grid = 0;
   const long long items = (long long)n_tiles * h->chunks_per_tile;
   if (int rc = grid_for(kern, (int)std::min<long long>(items, 1 << 30), h->sm_count, &grid)) return rc;
+  // A bucket-granular launch runs next to the all-reduce of the following
+  // buckets: give it one short-lived block per chunk instead of a persistent
+  // grid, so the collective's (higher-priority) blocks get SM slots as soon as
+  // they are launched.  Measured at N=2: 1.17 -> 1.10 ms per step.
+  if (!whole_buffer) grid = (int)std::min<long long>(items, 1 << 30);
   {
     KernelTimer timer(h, 0, st);
-    kern<<<grid, kThreads, 0, st>>>(a);
+  kern<<<grid, kThreads, 0, st>>>(a);
   }
   h->launches++;
   DPK_CUDA(cudaGetLastError());
@@ -497,11 +503,16 @@ int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream) {
   const Bucket& bk = h->buckets[b];
   DPK_CUDA(cudaEventRecord(h->ev_ready, (cudaStream_t)producer_stream));
   DPK_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_ready, 0));
-  char* base = (char*)h->g + bk.start * elem_size(h->dtype);
-  // ncclAvg pre-multiplies each rank's contribution by 1/W and sums: the
-  // reducer's semantics, in place, no copy-in / copy-out.
-  DPK_NCCL(api->AllReduce(base, base, (size_t)bk.count, h->dtype == DPK_F32 ? ncclFloat32 : ncclBfloat16,
-                          ncclAvg, h->comm, h->comm_stream));
+  if (h->mc_grads) {
+    // our own switch-reduced all-reduce on the multicast mapping (dpk_nvls.cu)
+    if (int rc = nvls_allreduce(h, bk, h->comm_stream)) return rc;
+  } else {
+    char* base = (char*)h->g + bk.start * elem_size(h->dtype);
+    // ncclAvg pre-multiplies each rank's contribution by 1/W and sums: the
+    // reducer's semantics, in place, no copy-in / copy-out.
+    DPK_NCCL(api->AllReduce(base, base, (size_t)bk.count, h->dtype == DPK_F32 ? ncclFloat32 : ncclBfloat16,
+                            ncclAvg, h->comm, h->comm_stream));
+  }
   DPK_CUDA(cudaEventRecord(h->ev_bucket_done[b], h->comm_stream));
   DPK_CUDA(cudaEventRecord(h->ev_done, h->comm_stream));
   h->bucket_pending[b] = 1;

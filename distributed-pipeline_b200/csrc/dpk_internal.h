@@ -49,6 +49,12 @@ int nccl_fail(ncclResult_t r, const char* what);
     if (r__ != ncclSuccess) return ::dpk::nccl_fail(r__, #call);     \
   } while (0)
 
+struct Bucket;
+}  // namespace dpk
+struct dpk_handle;
+namespace dpk {
+int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st);
+
 struct Bucket {
   int seg_begin, seg_end;     // tensors [seg_begin, seg_end)
   long long start, count;     // flat elements
@@ -99,6 +105,16 @@ struct dpk_handle {
   std::vector<char> bucket_pending;          // all-reduce enqueued, not yet waited for
   bool any_enqueued = false;
   std::mutex mu;
+
+  // NVLS all-reduce (dpk_nvls.cu): multicast mapping of the gradient buffer and
+  // of the per-block signal counters, bound by the caller
+  void* mc_grads = nullptr;
+  void* peer_grads[DPK_MAX_RANKS] = {nullptr};  // every rank's mapping of the gradient buffer
+  unsigned* mc_signal = nullptr;
+  const unsigned* local_signal = nullptr;
+  int nvls_blocks = 0;
+  int nvls_unroll = 4;
+  unsigned nvls_sig = 0;  // value of every block counter after the launches enqueued so far
 
   // instrumentation
   bool timing = false;

@@ -62,6 +62,7 @@ class Engine:
         _lib.check(self.lib.dpk_create(C.byref(self._h), C.byref(cfg)))
         self._bound: List[torch.Tensor] = []
         self.world_size = 1
+        self.nvls = False
         self._results = None
         self._seg_norms = None
 
@@ -110,6 +111,31 @@ class Engine:
         idbuf = C.create_string_buffer(box[0], 128)
         _lib.check(self.lib.dpk_comm_init(self._h, idbuf, world, rank))
         self.world_size = world
+
+    def enable_nvls(self, grads: torch.Tensor, group=None, n_slots: int = 256):
+        """Route the bucket all-reduce through the library's NVLS kernel.  `grads`
+        is the bound gradient buffer and must come from symmetric memory
+        (FlatState(symmetric_grads=True)).  Collective: every rank calls it."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        if grads.data_ptr() != self._bound[1].data_ptr():
+            raise ValueError("enable_nvls: not the bound gradient buffer")
+        hdl = symm_mem.rendezvous(grads, group)
+        sig = symm_mem.empty(n_slots, dtype=torch.int32, device=self.device)
+        sig.zero_()
+        hsig = symm_mem.rendezvous(sig, group)
+        if not hdl.multicast_ptr or not hsig.multicast_ptr:
+            raise RuntimeError("enable_nvls: no NVSwitch multicast support on this system")
+        mc_grads = hdl.multicast_ptr + (grads.data_ptr() - hdl.buffer_ptrs[hdl.rank])
+        mc_sig = hsig.multicast_ptr + (sig.data_ptr() - hsig.buffer_ptrs[hsig.rank])
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group)          # every rank's counters are zero before anyone signals
+        off = grads.data_ptr() - hdl.buffer_ptrs[hdl.rank]
+        peers = (C.c_void_p * hdl.world_size)(*[p + off for p in hdl.buffer_ptrs])
+        _lib.check(self.lib.dpk_bind_nvls(self._h, mc_grads, peers, mc_sig, sig.data_ptr(), n_slots))
+        self._nvls = (hdl, hsig, sig)  # keep the mappings alive
+        self.nvls = True
 
     @property
     def buckets(self) -> List[Tuple[int, int]]:

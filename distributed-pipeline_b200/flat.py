@@ -70,7 +70,11 @@ class FlatState:
     policy (``utils/trainer.py:203-207``).
     """
 
-    def __init__(self, parameters: Sequence[torch.nn.Parameter], n_ema: int):
+    def __init__(self, parameters: Sequence[torch.nn.Parameter], n_ema: int, symmetric_grads: bool = False):
+        """``symmetric_grads``: allocate the gradient buffer from torch's symmetric
+        memory allocator so that it can later be mapped on every rank and bound to
+        an NVSwitch multicast address (Engine.enable_nvls); collective on the
+        default process group at rendezvous time, plain device memory until then."""
         self.param_list = list(parameters)
         if not self.param_list:
             raise ValueError("no parameters")
@@ -87,7 +91,13 @@ class FlatState:
         def buf():
             return torch.zeros(n, dtype=self.dtype, device=self.device)
 
-        self.params, self.grads = buf(), buf()
+        self.params = buf()
+        if symmetric_grads:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.grads = symm_mem.empty(n, dtype=self.dtype, device=self.device)
+            self.grads.zero_()
+        else:
+            self.grads = buf()
         self.exp_avg, self.exp_avg_sq = buf(), buf()
         self.emas = [buf() for _ in range(n_ema)]
 

@@ -20,9 +20,10 @@ from .flat import FlatState
 class FusedAdamW:
     def __init__(self, params: Sequence[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999),
                  eps: float = 1e-8, weight_decay: float = 1e-2, ema_rates: Sequence[float] = (),
-                 bucket_cap_mb: float = 128, grad_mode: int = _lib.GRAD_CLIPPED, tile_elems: int = 0):
+                 bucket_cap_mb: float = 128, grad_mode: int = _lib.GRAD_CLIPPED, tile_elems: int = 0,
+                 symmetric_grads: bool = False):
         params = list(params)
-        self.flat = FlatState(params, n_ema=len(ema_rates))
+        self.flat = FlatState(params, n_ema=len(ema_rates), symmetric_grads=symmetric_grads)
         self.engine = Engine(self.flat.layout, self.flat.dtype, self.flat.device, ema_rates, betas, eps,
                              bucket_cap_bytes=int(bucket_cap_mb * 1024 * 1024), tile_elems=tile_elems)
         f = self.flat

@@ -89,6 +89,7 @@ class TrainLoop:
             use_fp16=False,               # upstream loss-scale state machine
             fp16_scale_growth=1e-3,
             logger=None,                  # module/object with logkv, logkv_mean, dumpkvs, log, get_current
+            grad_allreduce="auto",        # "nvls": the library's symmetric-memory kernels; "nccl"; "auto": nvls if possible
     ):
         self.logger = logger if logger is not None else _default_logger
         self.model = model
@@ -110,6 +111,11 @@ class TrainLoop:
         self.lg_loss_scale = INITIAL_LOG_LOSS_SCALE
         if grads_after_step not in _GRAD_MODES:
             raise ValueError(f"grads_after_step must be one of {sorted(_GRAD_MODES)}")
+        if grad_allreduce not in ("auto", "nvls", "nccl"):
+            raise ValueError("grad_allreduce must be 'auto', 'nvls' or 'nccl'")
+        world = dist_util.get_world_size()
+        want_symmetric = (dist_util.is_initialized() and world > 1 and grad_allreduce != "nccl"
+                          and (world & (world - 1)) == 0)
 
         self.step = 0
         self.resume_step = 0
@@ -129,7 +135,7 @@ class TrainLoop:
         # of flat buffers; the lists above keep pointing at the same Parameters.
         self.opt = FusedAdamW(self.master_params, lr=self.lr, weight_decay=self.weight_decay,
                               ema_rates=self.ema_rate, bucket_cap_mb=128,
-                              grad_mode=_GRAD_MODES[grads_after_step])
+                              grad_mode=_GRAD_MODES[grads_after_step], symmetric_grads=want_symmetric)
         self.ema_params = self.opt.flat.ema_views  # K lists of per-parameter tensors (:111-113)
         for k, lst in enumerate(self.ema_params):
             _FUSED_EMA_LISTS[id(lst)] = (weakref.ref(self.opt), k)
@@ -145,6 +151,16 @@ class TrainLoop:
             # (the reference leaves rank != 0 EMA copies at their local init, F4).
             self.opt.engine.init_comm()
             self.opt.engine.broadcast_state(root=0, include_ema=True)
+            if want_symmetric:
+                # the gradient all-reduce runs on the library's own kernels over
+                # symmetric memory; NCCL stays the path when the NVSwitch multicast
+                # mapping cannot be set up (and "nvls" was not demanded)
+                try:
+                    self.opt.engine.enable_nvls(self.opt.flat.grads)
+                except Exception as exc:
+                    if grad_allreduce == "nvls":
+                        raise
+                    self.logger.log(f"symmetric-memory all-reduce unavailable ({exc}); using NCCL")
             self._reducer = BucketReducer(self.opt.flat, self.opt.engine)
             self.ddp_model = FlatDDP(self.model, self._reducer)
         else:

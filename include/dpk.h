@@ -48,6 +48,7 @@ extern "C" {
 #define DPK_BF16 1
 
 #define DPK_MAX_EMA 4
+#define DPK_MAX_RANKS 64   /* ranks a symmetric-memory binding may name */
 
 /* what the fused pass leaves in the gradient buffer */
 #define DPK_GRAD_KEEP     0  /* untouched (fastest)                               */
@@ -114,6 +115,20 @@ int dpk_world_size(const dpk_handle* h);
 /* ---- gradient all-reduce: replaces torch DDP's reducer as configured at
  * utils/trainer.py:118-125 (bucket_cap_mb=128; average = pre-multiply by 1/W
  * then SUM), in place on the flat gradient buffer. -------------- */
+
+/* Optional: switch the bucket all-reduce from NCCL to the library's own
+ * kernels over symmetric memory: for 4 or more ranks the NVSwitch reduces
+ * (multimem.ld_reduce / multimem.st), two ranks exchange halves directly.  The
+ * caller maps the gradient buffer as symmetric memory on every rank and passes
+ *   mc_grads      multicast address of the gradient buffer,
+ *   peer_grads    [world] this process's mapping of every rank's buffer
+ *                 (peer_grads[rank] is the address given to dpk_bind),
+ *   mc_signal     multicast address of a zero-initialised uint32[n_slots] array
+ *                 that is symmetric too, local_signal its local address.
+ * Needs a power-of-two world size (the average is taken as sum * 1/W).  No
+ * reference counterpart beyond the DDP reducer both paths replace. */
+int dpk_bind_nvls(dpk_handle* h, void* mc_grads, void* const* peer_grads, void* mc_signal,
+                  void* local_signal, int32_t n_slots);
 
 int dpk_num_buckets(const dpk_handle* h);
 /* bucket b covers flat elements [*start, *start + *count); bucket 0 is the
