@@ -249,7 +249,12 @@ def run_ours(args):
         eng.init_comm()
         eng.broadcast_state(0, True)
         if args.allreduce == "nvls":
-            eng.enable_nvls(flat.grads)
+            try:
+                eng.enable_nvls(flat.grads)
+            except Exception as exc:  # no NVSwitch multicast on this box: NCCL carries the all-reduce
+                if rank == 0:
+                    print(f"[bench] symmetric-memory all-reduce unavailable ({exc}); using NCCL", file=sys.stderr)
+                args.allreduce = "nccl"
     ggen = torch.Generator(device=dev).manual_seed(4321 + rank)
     sigma = 1e-3
     grads_src = (torch.randn(flat.layout.n_elems, generator=ggen, device=dev) * sigma).to(tdt)
@@ -296,7 +301,8 @@ def run_ours(args):
         t = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms = float(t.item())
-        launches += n_buckets * args.steps  # NCCL all-reduce kernels we enqueue
+        if not eng.nvls:
+            launches += n_buckets * args.steps  # ncclAllReduce kernels we enqueue (ours are counted by the library)
     ms_per_step = elapsed_ms / args.steps
     bpp = bytes_per_param(dtype, len(rates), clip, args.grad_mode)
     value = world * n_params * bpp / (ms_per_step * 1e-3) / 1e9
@@ -386,7 +392,8 @@ def run_ours(args):
                        "l2_policy": f"inputs larger than L2 ({n_params * bpp / 1e6:.0f} MB streamed per step vs 126 MB L2)",
                        "allreduce_buckets": n_buckets if world > 1 else 0,
                        "bucket_mb": args.bucket_mb if world > 1 else None,
-                       "allreduce": (args.allreduce if world > 1 else None),
+                       "allreduce": (("own kernels over symmetric memory (NVLS multimem for W>=4, pair exchange for W=2)"
+                                      if eng.nvls else "ncclAllReduce(avg)") if world > 1 else None),
                        "update_overlaps_allreduce": bool(world > 1 and not args.no_overlap),
                        "grad_sigma": sigma},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
