@@ -502,7 +502,7 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
 // descriptor of the next item is fetched while the current one is processed.
 // resident blocks per SM the register allocation is asked to allow
 template <typename T, int K>
-constexpr int update_min_blocks() { return sizeof(T) == 4 ? (K <= 2 ? 4 : 3) : (K <= 2 ? 3 : 2); }
+constexpr int update_min_blocks() { return sizeof(T) == 4 ? (K <= 2 ? 4 : 3) : (K <= 2 ? 4 : 3); }
 
 template <typename T, int K, int GM>
 __global__ void __launch_bounds__(kThreads, update_min_blocks<T, K>())
