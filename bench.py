@@ -49,7 +49,7 @@ def parse_args():
                     help="sweep mode: one flat tensor of this many parameters instead of the model shapes")
     ap.add_argument("--grad-mode", default="keep", choices=["keep", "clipped", "zero"])
     ap.add_argument("--tile-elems", type=int, default=0)
-    ap.add_argument("--bucket-mb", type=float, default=128.0,
+    ap.add_argument("--bucket-mb", type=float, default=64.0,
                     help="all-reduce bucket size for N>1 (reference DDP: 128; results do not depend on it)")
     ap.add_argument("--allreduce", choices=["nvls", "nccl"], default="nvls",
                     help="N>1: the library's own NVLS (multimem) all-reduce kernel, or ncclAllReduce")

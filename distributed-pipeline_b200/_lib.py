@@ -23,6 +23,7 @@ GRAD_KEEP, GRAD_CLIPPED, GRAD_ZERO = 0, 1, 2
 R_TOTAL_NORM, R_CLIP_COEF, R_LOGGED_NORM, R_NONFINITE, R_SKIPPED, R_COUNT = 0, 1, 2, 3, 4, 8
 E_BADARG, E_NCCL, E_STATE, E_NOMEM, E_LIMIT = -1, -2, -3, -4, -5
 STATIC_MAX_ELEMS = 536870912
+OPT_OVERLAP_BLOCKS_PER_SM = 1
 
 
 class DpkError(RuntimeError):
@@ -47,6 +48,7 @@ class Config(C.Structure):
         ("beta2", C.c_double),
         ("eps", C.c_double),
         ("bucket_cap_bytes", C.c_int64),
+        ("edge_bucket_bytes", C.c_int64),
     ]
 
 
@@ -78,6 +80,7 @@ SIGNATURES = {
     "dpk_fused_update_bucket": (C.c_int, [_VP, C.c_int32, C.c_double, C.c_double, C.c_int64, C.c_double, C.c_int32,
                                            C.c_int32, C.c_int32, _VP]),
     "dpk_fused_update_finish": (C.c_int, [_VP, C.c_int32, _VP]),
+    "dpk_set_option": (C.c_int, [_VP, C.c_int32, C.c_int64]),
     "dpk_result_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),
     "dpk_read_result_sync": (C.c_int, [_VP, C.POINTER(C.c_double), _VP]),
     "dpk_segment_norms_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),

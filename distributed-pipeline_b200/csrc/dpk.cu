@@ -190,7 +190,10 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   // buckets: give it one short-lived block per chunk instead of a persistent
   // grid, so the collective's (higher-priority) blocks get SM slots as soon as
   // they are launched.  Measured at N=2: 1.17 -> 1.10 ms per step.
-  if (!whole_buffer) grid = (int)std::min<long long>(items, 1 << 30);
+  if (!whole_buffer)
+    grid = h->overlap_blocks_per_sm > 0
+               ? (int)std::min<long long>(items, (long long)h->overlap_blocks_per_sm * h->sm_count)
+               : (int)std::min<long long>(items, 1 << 30);
   {
     KernelTimer timer(h, 0, st);
   kern<<<grid, kThreads, 0, st>>>(a);
@@ -384,24 +387,46 @@ int dpk_create(dpk_handle** out, const dpk_config* cfg) {
   h->seg_tile_begin[h->n_seg] = (int)h->tiles.size();
 
   // buckets: walk tensors from the last (first gradient ready) to the first,
-  // closing a bucket once it reaches the cap -- DDP's rebuilt-bucket policy.
+  // closing a bucket once it reaches the cap -- DDP's rebuilt-bucket policy --
+  // except that the first bucket (tail) and the last one (head) are small: the
+  // first all-reduce has nothing to run beside yet, and nothing is left to hide
+  // the last bucket's consumer behind.
   {
     const long long cap = cfg->bucket_cap_bytes > 0 ? cfg->bucket_cap_bytes : (128LL << 20);
+    const long long last_cap = cfg->edge_bucket_bytes > 0 ? cfg->edge_bucket_bytes : cap / 8;
+    bool first = last_cap < cap;  // the first bucket closes early
     const int es = elem_size(h->dtype);
+    auto push = [&](int seg_begin, int seg_end) {
+      Bucket b;
+      b.seg_begin = seg_begin;
+      b.seg_end = seg_end;
+      b.start = h->seg_off[seg_begin];
+      const long long end = (seg_end == h->n_seg) ? h->n_elems : h->seg_off[seg_end];
+      b.count = end - b.start;
+      b.tile_begin = h->seg_tile_begin[seg_begin];
+      b.tile_end = h->seg_tile_begin[seg_end];
+      h->buckets.push_back(b);
+    };
     int seg_end = h->n_seg;
     long long bytes = 0;
     for (int s = h->n_seg - 1; s >= 0; --s) {
       bytes += h->seg_len[s] * es;
-      if (bytes >= cap || s == 0) {
-        Bucket b;
-        b.seg_begin = s;
-        b.seg_end = seg_end;
-        b.start = h->seg_off[s];
-        const long long end = (seg_end == h->n_seg) ? h->n_elems : h->seg_off[seg_end];
-        b.count = end - b.start;
-        b.tile_begin = h->seg_tile_begin[s];
-        b.tile_end = h->seg_tile_begin[seg_end];
-        h->buckets.push_back(b);
+      if (bytes >= (first ? last_cap : cap) || s == 0) {
+        first = false;
+        if (s == 0 && last_cap < cap && bytes > 2 * last_cap) {
+          // head bucket [0, seg_end): cut at the first tensor boundary past last_cap
+          long long head = 0;
+          int cut = 0;
+          while (cut < seg_end - 1 && head < last_cap) head += h->seg_len[cut++] * es;
+          if (cut > 0 && cut < seg_end && head < bytes) {
+            push(cut, seg_end);
+            push(0, cut);
+          } else {
+            push(0, seg_end);
+          }
+        } else {
+          push(s, seg_end);
+        }
         seg_end = s;
         bytes = 0;
       }
@@ -685,6 +710,19 @@ int dpk_fused_update(dpk_handle* h, double lr, double weight_decay, int64_t adam
                                        skip_if_nonfinite, grad_mode, stream))
     return rc;
   return dpk_fused_update_finish(h, skip_if_nonfinite, stream);
+}
+
+int dpk_set_option(dpk_handle* h, int32_t option, int64_t value) {
+  if (!h) { set_error("dpk_set_option: null handle"); return DPK_E_BADARG; }
+  switch (option) {
+    case DPK_OPT_OVERLAP_BLOCKS_PER_SM:
+      if (value < 0 || value > 32) { set_error("dpk_set_option: blocks per SM must be in 0..32"); return DPK_E_BADARG; }
+      h->overlap_blocks_per_sm = (int)value;
+      return 0;
+    default:
+      set_error("dpk_set_option: unknown option %d", option);
+      return DPK_E_BADARG;
+  }
 }
 
 int dpk_result_ptr(dpk_handle* h, void** d_out) {

@@ -32,7 +32,7 @@ class _DeviceArray:
 class Engine:
     def __init__(self, layout: FlatLayout, dtype: torch.dtype, device: torch.device,
                  ema_rates: Sequence[float] = (), betas=(0.9, 0.999), eps: float = 1e-8,
-                 bucket_cap_bytes: int = 128 << 20, tile_elems: int = 0):
+                 bucket_cap_bytes: int = 128 << 20, tile_elems: int = 0, edge_bucket_bytes: int = 0):
         device = torch.device(device)
         if device.type != "cuda":
             raise RuntimeError(
@@ -58,7 +58,8 @@ class Engine:
             device=device.index,
             n_segments=n_seg, n_ema=len(self.ema_rates), tile_elems=tile_elems, n_elems=layout.n_elems,
             seg_offsets=offs, seg_numel=nums, ema_rates=rates,
-            beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, bucket_cap_bytes=bucket_cap_bytes)
+            beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, bucket_cap_bytes=bucket_cap_bytes,
+            edge_bucket_bytes=edge_bucket_bytes)
         _lib.check(self.lib.dpk_create(C.byref(self._h), C.byref(cfg)))
         self._bound: List[torch.Tensor] = []
         self.world_size = 1
@@ -210,6 +211,9 @@ class Engine:
                 self._seg_norms = torch.as_tensor(_DeviceArray(p.value, (n,), "<f8", self), device=self.device)
         return self._seg_norms[:len(self.layout.offsets)]
 
+    def set_option(self, option: int, value: int):
+        _lib.check(self.lib.dpk_set_option(self._h, option, value))
+
     # -- instrumentation -------------------------------------------------------
     def timing(self, on: bool):
         _lib.check(self.lib.dpk_timing_enable(self._h, int(on)))
@@ -247,7 +251,8 @@ def ema_update(target: torch.Tensor, source: torch.Tensor, rate: float, stream=N
                                              _stream_ptr(stream, target.device)))
 
 
-def plan_buckets(layout: FlatLayout, dtype: torch.dtype, bucket_cap_bytes: int = 128 << 20) -> List[Tuple[int, int]]:
+def plan_buckets(layout: FlatLayout, dtype: torch.dtype, bucket_cap_bytes: int = 128 << 20,
+                 edge_bucket_bytes: int = 0) -> List[Tuple[int, int]]:
     """The library's all-reduce bucket plan for a layout, as (start, count) flat
     element ranges, tail first.  Host-only: works without a GPU."""
     lib = _lib.lib()
@@ -256,7 +261,8 @@ def plan_buckets(layout: FlatLayout, dtype: torch.dtype, bucket_cap_bytes: int =
     nums = (C.c_int64 * max(n_seg, 1))(*layout.numels)
     cfg = _lib.Config(abi_version=_lib.ABI_VERSION, dtype=dtype_code(dtype), device=0, n_segments=n_seg, n_ema=0,
                       tile_elems=0, n_elems=layout.n_elems, seg_offsets=offs, seg_numel=nums, ema_rates=None,
-                      beta1=0.9, beta2=0.999, eps=1e-8, bucket_cap_bytes=bucket_cap_bytes)
+                      beta1=0.9, beta2=0.999, eps=1e-8, bucket_cap_bytes=bucket_cap_bytes,
+                      edge_bucket_bytes=edge_bucket_bytes)
     h = C.c_void_p()
     _lib.check(lib.dpk_create(C.byref(h), C.byref(cfg)))
     try:

@@ -82,6 +82,13 @@ typedef struct dpk_config {
   const double* ema_rates;  /* [n_ema] as parsed by TrainLoop (:72-76)          */
   double beta1, beta2, eps; /* AdamW defaults of the reference: .9, .999, 1e-8  */
   int64_t bucket_cap_bytes; /* all-reduce bucket size; reference: 128 MiB (:123) */
+  int64_t edge_bucket_bytes; /* size of the FIRST bucket (the tail of the buffer: its
+                                all-reduce starts with nothing to run beside it yet)
+                                and of the LAST one (the head: nothing is left to hide
+                                its consumer behind).  Both are kept small; torch DDP
+                                does the same for its first bucket.  0 = cap/8;
+                                >= cap: plain cap-sized buckets.  Results do not
+                                depend on the bucket plan. */
 } dpk_config;
 
 /* ---- library ---------------------------------------------------------- */
@@ -191,6 +198,15 @@ int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double wei
                             int64_t adam_step, double inv_scale, int32_t use_clip_coef,
                             int32_t skip_if_nonfinite, int32_t grad_mode, void* stream);
 int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stream);
+
+/* Tuning knobs (never change results).
+ *   DPK_OPT_OVERLAP_BLOCKS_PER_SM  grid of a bucket-granular update launch, which
+ *       runs beside the all-reduce of later buckets: 0 = one short-lived block
+ *       per 4 KiB chunk; n > 0 = a persistent grid of n blocks per SM, i.e. a
+ *       deliberately throttled update that leaves HBM bandwidth to the
+ *       collective when the step is NVLink-bound. */
+#define DPK_OPT_OVERLAP_BLOCKS_PER_SM 1
+int dpk_set_option(dpk_handle* h, int32_t option, int64_t value);
 
 /* Device address of the result block (DPK_R_COUNT doubles). */
 int dpk_result_ptr(dpk_handle* h, void** d_out);

@@ -46,7 +46,7 @@ def _cfg(offsets, numels, n_elems, dtype=0, n_ema=0, tile=0, abi=_lib.ABI_VERSIO
     keep = ((C.c_int64 * max(n, 1))(*offsets), (C.c_int64 * max(n, 1))(*numels), (C.c_double * 4)(0.9, 0.9, 0.9, 0.9))
     cfg = _lib.Config(abi_version=abi, dtype=dtype, device=0, n_segments=n, n_ema=n_ema, tile_elems=tile,
                       n_elems=n_elems, seg_offsets=keep[0], seg_numel=keep[1], ema_rates=keep[2], beta1=0.9,
-                      beta2=0.999, eps=1e-8, bucket_cap_bytes=0)
+                      beta2=0.999, eps=1e-8, bucket_cap_bytes=0, edge_bucket_bytes=0)
     return cfg, keep
 
 
@@ -87,6 +87,16 @@ def test_calls_before_bind_report_state_error():
     assert lib.dpk_zero_grads(h, None) == _lib.E_STATE
     assert b"not bound" in lib.dpk_last_error()
     assert lib.dpk_world_size(h) == 1
+    # options and the symmetric-memory binding validate their arguments without a device
+    assert lib.dpk_set_option(h, _lib.OPT_OVERLAP_BLOCKS_PER_SM, 2) == 0
+    assert lib.dpk_set_option(h, _lib.OPT_OVERLAP_BLOCKS_PER_SM, -1) == _lib.E_BADARG
+    assert lib.dpk_set_option(h, 99, 0) == _lib.E_BADARG
+    assert lib.dpk_bind_nvls(h, None, None, None, None, 0) == _lib.E_BADARG
+    ptrs = (C.c_void_p * 2)(16, 32)
+    assert lib.dpk_bind_nvls(h, 16, ptrs, 16, 16, 8) == _lib.E_STATE      # not bound, single rank
+    assert lib.dpk_wait_bucket(h, 7, None) == _lib.E_BADARG
+    assert lib.dpk_grad_norm_bucket(h, 0, 1.0, None) == _lib.E_STATE
+    assert lib.dpk_fused_update_finish(h, 0, None) == _lib.E_STATE
     assert lib.dpk_destroy(h) == 0
     with pytest.raises(_lib.DpkError):
         _lib.check(lib.dpk_grad_norm(None, 1.0, 1.0, None))
@@ -95,7 +105,7 @@ def test_calls_before_bind_report_state_error():
 def test_bucket_plan_tail_first_and_capped():
     # 4-byte elements; cap 1000 bytes -> a bucket closes once it holds >= 250 elements
     lay = FlatLayout.from_numels([100, 300, 10, 10, 500, 20], 4)
-    ranges = plan_buckets(lay, __import__("torch").float32, bucket_cap_bytes=1000)
+    ranges = plan_buckets(lay, __import__("torch").float32, bucket_cap_bytes=1000, edge_bucket_bytes=1000)
     # walk from the last tensor: [20,500] closes (520>=250); [10,10,300] closes; [100] is what is left
     assert ranges[0][0] == lay.offsets[4] and ranges[0][0] + ranges[0][1] == lay.n_elems
     assert ranges[1] == (lay.offsets[1], lay.offsets[4] - lay.offsets[1])
@@ -106,9 +116,20 @@ def test_bucket_plan_tail_first_and_capped():
     for (s0, c0), (s1, _) in zip(covered, covered[1:]):
         assert s0 + c0 == s1
     assert covered[-1][0] + covered[-1][1] == lay.n_elems
-    # DiffuSeq-base at the reference's 128 MiB cap: 3 buckets fp32, 2 bf16
+    # DiffuSeq-base at the reference's 128 MiB cap: 3 buckets fp32, 2 bf16, like DDP's rebuilt
+    # buckets ...
     import torch
     from distributed_pipeline_b200.synthetic import diffuseq_shapes, numel
     numels = [numel(s) for s in diffuseq_shapes()]
-    assert len(plan_buckets(FlatLayout.from_numels(numels, 4), torch.float32)) == 3
-    assert len(plan_buckets(FlatLayout.from_numels(numels, 2), torch.bfloat16)) == 2
+    cap = 128 << 20
+    lay4, lay2 = FlatLayout.from_numels(numels, 4), FlatLayout.from_numels(numels, 2)
+    assert len(plan_buckets(lay4, torch.float32, cap, edge_bucket_bytes=cap)) == 3
+    assert len(plan_buckets(lay2, torch.bfloat16, cap, edge_bucket_bytes=cap)) == 2
+    # ... plus, by default, a small first bucket (tail) and a small last one (head)
+    r4 = plan_buckets(lay4, torch.float32)
+    assert len(r4) == 5 and r4[-1][0] == 0 and 16 << 20 <= r4[-1][1] * 4 <= 32 << 20
+    assert r4[0][0] + r4[0][1] == lay4.n_elems and 16 << 20 <= r4[0][1] * 4 <= 32 << 20
+    assert sorted(r4)[0][0] == 0 and sum(c for _, c in r4) == lay4.n_elems
+    # the split never produces an empty or out-of-order bucket
+    tiny = plan_buckets(FlatLayout.from_numels([10, 10, 10], 4), torch.float32, bucket_cap_bytes=1 << 20)
+    assert tiny == [(0, FlatLayout.from_numels([10, 10, 10], 4).n_elems)]
