@@ -198,35 +198,32 @@ __device__ __forceinline__ double block_sum_f64(double v, double* smem) {
   return r;
 }
 
-// ------------------------------------------------------- pass 1: sum sq ----
-// Reads g once (s bytes/param).  One partial per tile.
-
+// One tile's sum of squares and non-finite indicator, per thread (the caller
+// reduces across the block).  Shared by the handle path and dpk_grad_norm_static
+// so that both add the same numbers in the same order.  Full vectors carry no
+// per-lane masking; the ragged last vector of a tensor belongs to the thread
+// that would own it anyway and is added last.  `tail_by_element`: read the ragged
+// tail element by element (the caller's array may end exactly there) instead of
+// as one masked 16-byte vector (flat buffers are padded).
 template <typename T, int U>
-__global__ void __launch_bounds__(kThreads)
-sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin,
-                   int tile_end, float inv_scale, TilePartial* __restrict__ partials) {
+__device__ __forceinline__ void tile_sumsq(const T* __restrict__ g_tile, int len, float inv_scale,
+                                           bool tail_by_element, float& acc, float& nonfin) {
   using Tr = ElemTraits<T>;
   constexpr int VE = Tr::VE;
-  __shared__ float red[kThreads / 32];
-  for (int t = tile_begin + blockIdx.x; t < tile_end; t += gridDim.x) {
-    const Tile tile = tiles[t];
-    const uint4* gv = reinterpret_cast<const uint4*>(g + tile.start);
-    const int nvec = (tile.len + VE - 1) / VE;
-    float acc = 0.f;
-    float nonfin = 0.f;
-    for (int v0 = threadIdx.x; v0 < nvec; v0 += kThreads * U) {
-      uint4 raw[U];
+  const uint4* gv = reinterpret_cast<const uint4*>(g_tile);
+  const int nfull = len / VE;
+  for (int v0 = threadIdx.x; v0 < nfull; v0 += kThreads * U) {
+    uint4 raw[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * kThreads;
-        raw[u] = (v < nvec) ? ld_readonly(gv + v) : make_uint4(0, 0, 0, 0);
-      }
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * kThreads;
+      raw[u] = (v < nfull) ? ld_readonly(gv + v) : make_uint4(0, 0, 0, 0);
+    }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * kThreads;
+    for (int u = 0; u < U; ++u) {
+      if (v0 + u * kThreads < nfull) {
         float x[VE];
         Tr::unpack(raw[u], x);
-        const int rem = tile.len - v * VE;  // valid lanes in this vector (<=0: none)
         if (inv_scale != 1.0f) {  // x*1 is exact: the unscale and its store only exist with a loss scale
 #pragma unroll
           for (int j = 0; j < VE; ++j) x[j] = __fmul_rn(x[j], inv_scale);
@@ -234,13 +231,44 @@ sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int 
         }
 #pragma unroll
         for (int j = 0; j < VE; ++j) {
-          if (j < rem) {
-            nonfin = __fmaf_rn(x[j], 0.0f, nonfin);  // stays 0 unless x is inf/nan, then NaN for good
-            acc = __fmaf_rn(x[j], x[j], acc);
-          }
+          nonfin = __fmaf_rn(x[j], 0.0f, nonfin);  // stays 0 unless x is inf/nan, then NaN for good
+          acc = __fmaf_rn(x[j], x[j], acc);
         }
       }
     }
+  }
+  const int rem = len - nfull * VE;
+  if (rem > 0 && (int)threadIdx.x == nfull % kThreads) {
+    float x[VE];
+    if (tail_by_element) {
+#pragma unroll
+      for (int j = 0; j < VE; ++j) x[j] = (j < rem) ? (float)g_tile[nfull * VE + j] : 0.f;
+    } else {
+      Tr::unpack(ld_readonly(gv + nfull), x);
+    }
+#pragma unroll
+    for (int j = 0; j < VE; ++j) {
+      if (j < rem) {
+        float y = x[j];
+        if (inv_scale != 1.0f) y = Tr::rnd(__fmul_rn(y, inv_scale));
+        nonfin = __fmaf_rn(y, 0.0f, nonfin);
+        acc = __fmaf_rn(y, y, acc);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------- pass 1: sum sq ----
+// Reads g once (s bytes/param).  One partial per tile.
+template <typename T, int U>
+__global__ void __launch_bounds__(kThreads)
+sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin,
+                   int tile_end, float inv_scale, TilePartial* __restrict__ partials) {
+  __shared__ float red[kThreads / 32];
+  for (int t = tile_begin + blockIdx.x; t < tile_end; t += gridDim.x) {
+    const Tile tile = tiles[t];
+    float acc = 0.f, nonfin = 0.f;
+    tile_sumsq<T, U>(g + tile.start, tile.len, inv_scale, false, acc, nonfin);
     const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
     const int any_bad = __syncthreads_or((int)bad);
     const float s = block_sum(acc, red);

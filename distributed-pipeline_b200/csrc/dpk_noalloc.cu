@@ -41,13 +41,11 @@ struct StaticScratch {
 static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
 
 // Streaming pass without a tile table: tile t covers [t*8192, min(n, (t+1)*8192)).
-// Inner loop order is sumsq_tiles_kernel's, so per-tile sums are identical.
+// tile_sumsq is the handle path's own inner loop, so per-tile sums are identical.
 template <typename T, int U>
 __global__ void __launch_bounds__(kThreads)
 sumsq_flat_kernel(const T* __restrict__ g, long long n, int n_tiles, float inv_scale,
                   StaticScratch* __restrict__ sc) {
-  using Tr = ElemTraits<T>;
-  constexpr int VE = Tr::VE;
   __shared__ float red[kThreads / 32];
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     sc->seg_tile_begin[0] = 0;
@@ -57,39 +55,10 @@ sumsq_flat_kernel(const T* __restrict__ g, long long n, int n_tiles, float inv_s
     const long long start = (long long)t * kStaticTileElems;
     const long long left = n - start;
     const int len = left < kStaticTileElems ? (int)left : kStaticTileElems;
-    const uint4* gv = reinterpret_cast<const uint4*>(g + start);
-    const int nvec = (len + VE - 1) / VE;
-    const int nfull = len / VE;  // the caller's array ends at n: a ragged last vector is read by element
-    float acc = 0.f;
-    unsigned bad = 0;
-    for (int v0 = threadIdx.x; v0 < nvec; v0 += kThreads * U) {
-      uint4 raw[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * kThreads;
-        raw[u] = (v < nfull) ? ld_readonly(gv + v) : make_uint4(0, 0, 0, 0);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * kThreads;
-        float x[VE];
-        Tr::unpack(raw[u], x);
-        const int rem = len - v * VE;
-        if (v == nfull && rem > 0) {
-#pragma unroll
-          for (int j = 0; j < VE; ++j)
-            if (j < rem) x[j] = (float)g[start + (long long)v * VE + j];
-        }
-#pragma unroll
-        for (int j = 0; j < VE; ++j) {
-          if (j < rem) {
-            const float y = Tr::rnd(__fmul_rn(x[j], inv_scale));
-            bad |= nonfinite_bits(y) ? 1u : 0u;
-            acc = __fmaf_rn(y, y, acc);
-          }
-        }
-      }
-    }
+    float acc = 0.f, nonfin = 0.f;
+    // the caller's array ends at n: a ragged last vector is read element by element
+    tile_sumsq<T, U>(g + start, len, inv_scale, true, acc, nonfin);
+    const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
     const int any_bad = __syncthreads_or((int)bad);
     const float s = block_sum(acc, red);
     if (threadIdx.x == 0) {
