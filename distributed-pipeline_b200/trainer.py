@@ -171,6 +171,11 @@ class TrainLoop:
         self._in_optimize = False
         self._norm_requested = False
         self._norm_inflight: List[tuple] = []
+        # pinned landing slots for the per-step result read-back (reused round-robin:
+        # allocating pinned memory every step would cost more than the update)
+        self._norm_ring = [(torch.empty(_lib.R_COUNT, dtype=torch.float64, pin_memory=True), torch.cuda.Event())
+                           for _ in range(16)]
+        self._norm_ring_pos = 0
         self._grads_are_zero = True  # fresh buffer
         torch.cuda.empty_cache()
 
@@ -356,20 +361,28 @@ class TrainLoop:
         if not self._norm_requested:
             return
         self._norm_requested = False
-        host = torch.empty(_lib.R_COUNT, dtype=torch.float64, pin_memory=True)
+        if len(self._norm_inflight) == len(self._norm_ring):
+            self._drain_norms(block=False, at_least=1)  # every slot is in flight: resolve the oldest first
+        host, ev = self._norm_ring[self._norm_ring_pos]
+        self._norm_ring_pos = (self._norm_ring_pos + 1) % len(self._norm_ring)
         host.copy_(self.opt.engine.results, non_blocking=True)
-        ev = torch.cuda.Event()
         ev.record()
         self._norm_inflight.append((ev, host))
 
-    def _drain_norms(self, block):
+    def _drain_norms(self, block, at_least=0):
+        """Feed finished read-backs to logger.logkv_mean("grad_norm", ...) -- the one
+        float per step the reference logs (utils/trainer.py:271) -- oldest first.
+        Waits for a read-back only if `block`, or until `at_least` have been resolved."""
+        done = 0
         while self._norm_inflight:
             ev, host = self._norm_inflight[0]
-            if not block and not ev.query():
-                break
-            ev.synchronize()
+            if not ev.query():
+                if not block and done >= at_least:
+                    break
+                ev.synchronize()
             self.logger.logkv_mean("grad_norm", float(host[_lib.R_LOGGED_NORM]))
             self._norm_inflight.pop(0)
+            done += 1
 
     def flush_logs(self):
         """Resolve every pending grad-norm read-back into the logger."""

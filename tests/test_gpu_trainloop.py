@@ -147,6 +147,37 @@ def test_checkpoints_are_torch_compatible_and_resume(tmp_path):
     assert loop2.opt.step_count == 3
 
 
+def test_run_loop_logs_and_saves_like_the_reference(tmp_path):
+    """run_loop (reference :175-196): dumpkvs every log_interval with step / samples /
+    mean grad_norm, final save; more steps than the read-back ring has slots."""
+    torch.manual_seed(102)
+    model = SyntheticDiffuSeq(**TOY).cuda()
+    data = batches(5, 8, n=40)
+    dumps = []
+    real_dump = logger.dumpkvs
+
+    class Spy:
+        def __getattr__(self, name):
+            return getattr(logger, name)
+
+        def dumpkvs(self):
+            out = real_dump()
+            dumps.append(out)
+            return out
+
+    loop = make_loop(model, data, tmp_path, learning_steps=36, log_interval=18, save_interval=1000, logger=Spy(),
+                     gradient_clipping=1.0)
+    loop.run_loop()
+    assert loop.step == 36
+    assert len(dumps) == 2                       # steps 0 and 18
+    assert dumps[0]["step"] == 0 and dumps[0]["samples"] == 8 and dumps[0]["grad_norm"] > 0
+    assert dumps[1]["step"] == 18 and dumps[1]["samples"] == 19 * 8
+    # clipped to 1.0 every step -> the logged post-clip norm is <= 1 (+ rounding)
+    assert 0 < dumps[1]["grad_norm"] <= 1.0 + 1e-5
+    assert (tmp_path / "model_000036.pt").exists() and (tmp_path / "opt_000036.pt").exists()
+    assert not loop._norm_inflight
+
+
 def test_update_ema_standalone_and_fused_flag(tmp_path):
     a = [torch.randn(100, device="cuda"), torch.randn(7, 3, device="cuda")]
     b = [torch.randn(100, device="cuda"), torch.randn(7, 3, device="cuda")]
