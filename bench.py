@@ -347,8 +347,7 @@ def run_ours(args):
         stream = torch.cuda.current_stream()
 
         def e2e_step():
-            flat.grads.copy_(host_g, non_blocking=True)
-            device_step()
+            opt.step_from_host(host_g, clip)     # upload, (all-reduce,) update: bucket by bucket
             host_res.copy_(results, non_blocking=True)
             stream.synchronize()
             return float(host_res[_lib.R_LOGGED_NORM])
@@ -372,7 +371,7 @@ def run_ours(args):
         e2e = {"value": world * n_params * bpp / (e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e_ms,
                "steps": e_steps, "h2d_bytes_per_step": host_g.numel() * host_g.element_size(),
                "d2h_bytes_per_step": host_res.numel() * host_res.element_size(), "last_grad_norm": norm,
-               "api": "FusedAdamW.clip_grad_norm/step (TrainLoop.opt) with host gradients"}
+               "api": "FusedAdamW.step_from_host (TrainLoop.opt): pinned host gradients, bucket-pipelined upload"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -97,6 +97,56 @@ class FusedAdamW:
         self._clip_pending = False
         self.ema_done = [True] * len(self.ema_rates)
 
+    @torch.no_grad()
+    def step_from_host(self, host_grads: torch.Tensor, max_norm: float = -1.0):
+        """One update whose gradients arrive from (pinned) host memory, laid out like
+        the flat gradient buffer.  The buffer is uploaded bucket by bucket on a copy
+        stream and every bucket is all-reduced (multi-rank) and consumed as soon as
+        it has landed, so the update hides behind the PCIe transfer of the next
+        bucket instead of following the whole copy."""
+        eng, flat = self.engine, self.flat
+        if host_grads.numel() != flat.layout.n_elems or host_grads.dtype != flat.dtype:
+            raise ValueError("host_grads must be a flat tensor with the layout of the gradient buffer")
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=flat.device)
+        cur = torch.cuda.current_stream(flat.device)
+        copy = self._copy_stream
+        copy.wait_stream(cur)                    # the previous step is done with the gradient buffer
+        buckets = eng.buckets
+        landed = []
+        with torch.cuda.stream(copy):
+            for b, (s, c) in enumerate(buckets):
+                flat.grads[s:s + c].copy_(host_grads[s:s + c], non_blocking=True)
+                if eng.world_size > 1:
+                    eng.bucket_ready(b, stream=copy)   # all-reduce follows the upload of this bucket
+                else:
+                    ev = torch.cuda.Event()
+                    ev.record(copy)
+                    landed.append(ev)
+        g = self.param_groups[0]
+
+        def arrived(b):
+            if eng.world_size > 1:
+                eng.wait_bucket(b)
+            else:
+                cur.wait_event(landed[b])
+
+        if max_norm > 0:
+            for b in range(len(buckets)):
+                arrived(b)
+                eng.grad_norm_bucket(b, self.inv_scale)
+            eng.grad_norm_finish(float(max_norm))
+            self._clip_pending = True
+            return self.step()
+        self.step_count += 1
+        for b in range(len(buckets)):
+            arrived(b)
+            eng.fused_update_bucket(b, float(g["lr"]), float(g["weight_decay"]), self.step_count,
+                                    inv_scale=self.inv_scale, grad_mode=self.grad_mode)
+        eng.fused_update_finish(False)
+        self._clip_pending = False
+        self.ema_done = [True] * len(self.ema_rates)
+
     def undo_step_count(self):
         """A predicated-off (non-finite) step must not advance AdamW's step."""
         self.step_count -= 1

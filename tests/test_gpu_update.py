@@ -228,3 +228,32 @@ def test_arithmetic_shortcuts_are_exact_for_every_input():
     for c in (0.3, 1.0, 0.7071067811865476, 0.0316, 0.999):
         _lib.check(lib.dpk_selftest_arith(c, out.data_ptr(), stream))
         assert out.cpu().tolist() == [0, 0], c
+
+
+@pytest.mark.parametrize("clip", [-1.0, 0.5])
+def test_step_from_host_equals_resident_step(clip):
+    """FusedAdamW.step_from_host (bucket-pipelined upload) == copy everything, then step."""
+    from distributed_pipeline_b200 import FusedAdamW
+    torch.manual_seed(3)
+    shapes = [(5000,), (3,), (300, 257), (128,), (9000,), (33,), (40000,)]
+
+    def make():
+        torch.manual_seed(3)
+        ps = [torch.nn.Parameter(torch.randn(s, device="cuda") * 0.02) for s in shapes]
+        return FusedAdamW(ps, lr=1e-3, weight_decay=0.01, ema_rates=[0.999], bucket_cap_mb=0.05, grad_mode=_lib.GRAD_KEEP)
+    a, b = make(), make()
+    assert len(a.engine.buckets) >= 3
+    host = torch.empty(a.flat.layout.n_elems, pin_memory=True)
+    for step in range(3):
+        host.normal_(0, 0.1)
+        a.step_from_host(host, clip)
+        b.flat.grads.copy_(host, non_blocking=True)
+        if clip > 0:
+            b.clip_grad_norm(clip)
+        b.step()
+        torch.cuda.synchronize()
+        assert a.engine.read_results_sync() == b.engine.read_results_sync()
+        for x, y in ((a.flat.params, b.flat.params), (a.flat.exp_avg, b.flat.exp_avg),
+                     (a.flat.exp_avg_sq, b.flat.exp_avg_sq), (a.flat.emas[0], b.flat.emas[0])):
+            assert torch.equal(x, y)
+    assert a.step_count == b.step_count == 3
