@@ -24,6 +24,7 @@ R_TOTAL_NORM, R_CLIP_COEF, R_LOGGED_NORM, R_NONFINITE, R_SKIPPED, R_COUNT = 0, 1
 E_BADARG, E_NCCL, E_STATE, E_NOMEM, E_LIMIT = -1, -2, -3, -4, -5
 STATIC_MAX_ELEMS = 536870912
 OPT_OVERLAP_BLOCKS_PER_SM = 1
+OPT_NORM_STAGING = 2
 
 
 class DpkError(RuntimeError):

@@ -138,6 +138,24 @@ static int launch_sumsq(dpk_handle* h, int tile_begin, int tile_end, float inv_s
                         cudaStream_t st) {
   const int n = tile_end - tile_begin;
   if (n <= 0) return 0;
+  if (h->norm_staging) {
+    // TMA-staged variant: kTmaStages tiles of shared memory per block
+    auto kern = sumsq_tiles_tma_kernel<T, 4>;
+    const int tile_bytes = h->tile_elems * (int)sizeof(T);
+    const int smem = kTmaStages * tile_bytes;
+    DPK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int occ = 0;
+    DPK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
+    const int grid = (int)std::max<long long>(1, std::min<long long>(n, (long long)std::max(occ, 1) * h->sm_count));
+    {
+      KernelTimer timer(h, 1, st);
+      kern<<<grid, kThreads, smem, st>>>((const T*)h->g, h->d_tiles, tile_begin, tile_end, tile_bytes, inv_scale,
+                                         h->d_partials_pre);
+    }
+    h->launches++;
+    DPK_CUDA(cudaGetLastError());
+    return 0;
+  }
   auto kern = sumsq_tiles_kernel<T, 4>;
   int grid = 0;
   if (int rc = grid_for(kern, n, h->sm_count, &grid)) return rc;
@@ -718,6 +736,14 @@ int dpk_set_option(dpk_handle* h, int32_t option, int64_t value) {
     case DPK_OPT_OVERLAP_BLOCKS_PER_SM:
       if (value < 0 || value > 32) { set_error("dpk_set_option: blocks per SM must be in 0..32"); return DPK_E_BADARG; }
       h->overlap_blocks_per_sm = (int)value;
+      return 0;
+    case DPK_OPT_NORM_STAGING:
+      if (value != 0 && value != 1) { set_error("dpk_set_option: staging is 0 or 1"); return DPK_E_BADARG; }
+      if (value && h->tile_elems * 4 * kTmaStages > 200 * 1024) {
+        set_error("dpk_set_option: tile of %d elements too large to stage %d deep in shared memory", h->tile_elems, kTmaStages);
+        return DPK_E_LIMIT;
+      }
+      h->norm_staging = (int)value;
       return 0;
     default:
       set_error("dpk_set_option: unknown option %d", option);

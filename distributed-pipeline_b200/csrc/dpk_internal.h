@@ -72,6 +72,7 @@ struct dpk_handle {
   int chunk_elems = 0;      // pass-2 work item; divides tile_elems
   int chunks_per_tile = 1;
   int overlap_blocks_per_sm = 0;  // DPK_OPT_OVERLAP_BLOCKS_PER_SM
+  int norm_staging = 0;           // DPK_OPT_NORM_STAGING
   long long n_elems = 0;
   double beta1 = 0.9, beta2 = 0.999, eps = 1e-8;
   double ema_rates[DPK_MAX_EMA] = {0};

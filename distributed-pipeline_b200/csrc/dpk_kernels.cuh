@@ -205,19 +205,21 @@ __device__ __forceinline__ double block_sum_f64(double v, double* smem) {
 // that would own it anyway and is added last.  `tail_by_element`: read the ragged
 // tail element by element (the caller's array may end exactly there) instead of
 // as one masked 16-byte vector (flat buffers are padded).
-template <typename T, int U>
+template <typename T, int U, bool STAGED = false>
 __device__ __forceinline__ void tile_sumsq(const T* __restrict__ g_tile, int len, float inv_scale,
                                            bool tail_by_element, float& acc, float& nonfin) {
   using Tr = ElemTraits<T>;
   constexpr int VE = Tr::VE;
   const uint4* gv = reinterpret_cast<const uint4*>(g_tile);
+  // STAGED: the tile already sits in shared memory (bulk-copied there), plain loads
+  auto ld = [](const uint4* p) { return STAGED ? *p : ld_readonly(p); };
   const int nfull = len / VE;
   for (int v0 = threadIdx.x; v0 < nfull; v0 += kThreads * U) {
     uint4 raw[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int v = v0 + u * kThreads;
-      raw[u] = (v < nfull) ? ld_readonly(gv + v) : make_uint4(0, 0, 0, 0);
+      raw[u] = (v < nfull) ? ld(gv + v) : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -244,7 +246,7 @@ __device__ __forceinline__ void tile_sumsq(const T* __restrict__ g_tile, int len
 #pragma unroll
       for (int j = 0; j < VE; ++j) x[j] = (j < rem) ? (float)g_tile[nfull * VE + j] : 0.f;
     } else {
-      Tr::unpack(ld_readonly(gv + nfull), x);
+      Tr::unpack(ld(gv + nfull), x);
     }
 #pragma unroll
     for (int j = 0; j < VE; ++j) {
@@ -275,6 +277,78 @@ sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int 
     if (threadIdx.x == 0) {
       TilePartial p;
       p.sumsq = s;
+      p.bad = any_bad ? 1u : 0u;
+      partials[t] = p;
+    }
+  }
+}
+
+// The same pass with the tiles staged through shared memory by the TMA engine:
+// one thread issues cp.async.bulk (1-D bulk tensor copy, SASS UBLKCP) for the
+// tile kStages-1 ahead and arms an mbarrier with the byte count; all threads wait
+// on the barrier's phase and sum from shared memory in tile_sumsq's order, so
+// the partials are bit-identical to the register path.  Selected with
+// DPK_OPT_NORM_STAGING; measured against the register path in DESIGN.md.
+constexpr int kTmaStages = 3;
+
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+template <typename T, int U>
+__global__ void __launch_bounds__(kThreads)
+sumsq_tiles_tma_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin, int tile_end,
+                       int tile_bytes_max, float inv_scale, TilePartial* __restrict__ partials) {
+  extern __shared__ __align__(128) unsigned char stage_mem[];
+  __shared__ __align__(8) unsigned long long full[kTmaStages];
+  __shared__ float red[kThreads / 32];
+  __shared__ Tile desc[kTmaStages];
+  constexpr int VE = ElemTraits<T>::VE;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < kTmaStages; ++s)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&full[s])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const int first = tile_begin + blockIdx.x;
+  auto issue = [&](int k) {  // thread 0: start the copy of this block's k-th tile into stage k % kTmaStages
+    const int t = first + k * gridDim.x;
+    if (t >= tile_end) return;
+    const int s = k % kTmaStages;
+    const Tile tile = tiles[t];
+    desc[s] = tile;
+    const unsigned bytes = (unsigned)(((tile.len + VE - 1) / VE) * 16);  // whole vectors; flat buffers are padded
+    const unsigned bar = smem_addr(&full[s]);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(stage_mem + (size_t)s * tile_bytes_max)), "l"(g + tile.start), "r"(bytes), "r"(bar)
+                 : "memory");
+  };
+  if (threadIdx.x == 0)
+    for (int k = 0; k < kTmaStages - 1; ++k) issue(k);
+
+  int k = 0;
+  for (int t = first; t < tile_end; t += gridDim.x, ++k) {
+    if (threadIdx.x == 0) issue(k + kTmaStages - 1);  // its stage was released by the barrier ending iteration k-1
+    const int s = k % kTmaStages;
+    const unsigned parity = (unsigned)(k / kTmaStages) & 1u;
+    const unsigned bar = smem_addr(&full[s]);
+    unsigned done = 0;
+    while (!done) {
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    }
+    const int len = desc[s].len;
+    float acc = 0.f, nonfin = 0.f;
+    tile_sumsq<T, U, true>(reinterpret_cast<const T*>(stage_mem + (size_t)s * tile_bytes_max), len, inv_scale, false,
+                           acc, nonfin);
+    const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
+    const int any_bad = __syncthreads_or((int)bad);  // also: every thread is done reading stage s
+    const float sum = block_sum(acc, red);
+    if (threadIdx.x == 0) {
+      TilePartial p;
+      p.sumsq = sum;
       p.bad = any_bad ? 1u : 0u;
       partials[t] = p;
     }

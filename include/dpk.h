@@ -204,8 +204,12 @@ int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stre
  *       runs beside the all-reduce of later buckets: 0 = one short-lived block
  *       per 4 KiB chunk; n > 0 = a persistent grid of n blocks per SM, i.e. a
  *       deliberately throttled update that leaves HBM bandwidth to the
- *       collective when the step is NVLink-bound. */
+ *       collective when the step is NVLink-bound.
+ *   DPK_OPT_NORM_STAGING  1 = the norm pass stages its tiles through shared
+ *       memory with TMA bulk copies (cp.async.bulk + mbarrier, 3 deep) instead of
+ *       128-bit register loads.  Same partial sums, bit for bit. */
 #define DPK_OPT_OVERLAP_BLOCKS_PER_SM 1
+#define DPK_OPT_NORM_STAGING 2
 int dpk_set_option(dpk_handle* h, int32_t option, int64_t value);
 
 /* Device address of the result block (DPK_R_COUNT doubles). */

@@ -42,4 +42,12 @@ for dtype, s in ((torch.float32, 4), (torch.bfloat16, 2)):
         t = sum(ms) / len(ms)
         if K == 0:
             print(f"{str(dtype):15s} sumsq            {t*1e3:7.1f} us  {n*s/t/1e6:7.0f} GB/s  frac={n*s/t/1e6/PEAK:.3f}", flush=True)
+            eng.set_option(_lib.OPT_NORM_STAGING, 1)
+            for _ in range(10):
+                eng.grad_norm(1.0, 1.0)
+            torch.cuda.synchronize()
+            ms = eng.read_timings_sync(1)[3:]
+            t = sum(ms) / len(ms)
+            print(f"{str(dtype):15s} sumsq (TMA)      {t*1e3:7.1f} us  {n*s/t/1e6:7.0f} GB/s  frac={n*s/t/1e6/PEAK:.3f}", flush=True)
+            eng.set_option(_lib.OPT_NORM_STAGING, 0)
         eng.close()

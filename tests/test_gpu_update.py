@@ -257,3 +257,24 @@ def test_step_from_host_equals_resident_step(clip):
                      (a.flat.exp_avg_sq, b.flat.exp_avg_sq), (a.flat.emas[0], b.flat.emas[0])):
             assert torch.equal(x, y)
     assert a.step_count == b.step_count == 3
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_tma_staged_norm_pass_is_bit_identical(dtype):
+    """DPK_OPT_NORM_STAGING: tiles bulk-copied to shared memory by the TMA engine; same sums, same bits."""
+    pb = FlatProblem(RAGGED + [100_000, 8192 * 5, 17], dtype, [], seed=21)
+    for inv_scale, max_norm in ((1.0, 1.0), (1.0 / 32, 0.5)):
+        g = pb.new_grads(std=0.7)
+        pb.engine.set_option(_lib.OPT_NORM_STAGING, 0)
+        pb.engine.grad_norm(inv_scale, max_norm)
+        a = pb.engine.read_results_sync()
+        seg_a = pb.engine.segment_norms.clone()
+        pb.engine.set_option(_lib.OPT_NORM_STAGING, 1)
+        pb.engine.grad_norm(inv_scale, max_norm)
+        b = pb.engine.read_results_sync()
+        assert a == b and torch.equal(seg_a, pb.engine.segment_norms)
+        ref = pb.oracle_norm(g, inv_scale, max_norm)
+        assert rel_err(b[_lib.R_TOTAL_NORM], ref["total"]) < (1e-5 if dtype == torch.float32 else 2 ** -7)
+    pb.g[pb.layout.offsets[-2] + 5] = float("nan")
+    pb.engine.grad_norm(1.0, 1.0)
+    assert pb.engine.read_results_sync()[_lib.R_NONFINITE] == 1.0
