@@ -20,7 +20,7 @@ ABI_VERSION = 1
 F32, BF16 = 0, 1
 MAX_EMA = 4
 GRAD_KEEP, GRAD_CLIPPED, GRAD_ZERO = 0, 1, 2
-R_TOTAL_NORM, R_CLIP_COEF, R_LOGGED_NORM, R_NONFINITE, R_SKIPPED, R_COUNT = 0, 1, 2, 3, 4, 8
+R_TOTAL_NORM, R_CLIP_COEF, R_LOGGED_NORM, R_NONFINITE, R_SKIPPED, R_COMM_TIMEOUT, R_COUNT = 0, 1, 2, 3, 4, 5, 8
 E_BADARG, E_NCCL, E_STATE, E_NOMEM, E_LIMIT = -1, -2, -3, -4, -5
 STATIC_MAX_ELEMS = 536870912
 OPT_OVERLAP_BLOCKS_PER_SM = 1

@@ -37,14 +37,31 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* addr) {
   return v;
 }
 
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+constexpr unsigned long long kPeerTimeoutNs = 30ull * 1000 * 1000 * 1000;  // a rank that is 30 s late is gone
+
 // All threads of the block call this.  `target` is the value this block's
-// counter reaches once all W ranks have arrived at this barrier.
-__device__ __forceinline__ void block_barrier_all_ranks(unsigned* mc_sig, const unsigned* local_sig, unsigned target) {
+// counter reaches once all W ranks have arrived at this barrier.  A peer that
+// never arrives (crashed rank) must not hang the GPU: after kPeerTimeoutNs the
+// wait is abandoned and the sticky DPK_R_COMM_TIMEOUT flag raised for the host.
+__device__ __forceinline__ void block_barrier_all_ranks(unsigned* mc_sig, const unsigned* local_sig, unsigned target,
+                                                        double* results) {
   __threadfence_system();  // this thread's multimem stores before the signal
   __syncthreads();
   if (threadIdx.x == 0) {
     mc_signal_add(mc_sig + blockIdx.x);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
     while ((int)(ld_acquire_sys(local_sig + blockIdx.x) - target) < 0) {
+      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > kPeerTimeoutNs) {
+        results[DPK_R_COMM_TIMEOUT] = 1.0;
+        break;
+      }
     }
   }
   __syncthreads();
@@ -94,9 +111,9 @@ __device__ __forceinline__ void multimem_st(uint4* mc, const uint4& v) {
 template <typename T, int kNvlsUnroll>
 __global__ void __launch_bounds__(kNvlsThreads)
 nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int rank, int world, float inv_world,
-                      unsigned* mc_sig, const unsigned* local_sig, unsigned sig_base) {
+                      unsigned* mc_sig, const unsigned* local_sig, unsigned sig_base, double* results) {
   // every rank's local gradients for this range are complete once its block b is here
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results);
 
   const long long per_rank = (n_vec + world - 1) / world;
   const long long lo = vec_begin + (long long)rank * per_rank;
@@ -114,7 +131,7 @@ nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int
   }
 
   // every rank's slice has been written into every copy once all block-b's are here
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u * (unsigned)world);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u * (unsigned)world, results);
 }
 
 // Two ranks: the switch has nothing to save (a multicast store also echoes the
@@ -148,8 +165,8 @@ __device__ __forceinline__ void st_peer(uint4* p, const uint4& v) {
 template <typename T, int U>
 __global__ void __launch_bounds__(kNvlsThreads)
 pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n_vec, int rank, unsigned* mc_sig,
-                      const unsigned* local_sig, unsigned sig_base) {
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u);
+                      const unsigned* local_sig, unsigned sig_base, double* results) {
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results);
   const long long per_rank = (n_vec + 1) / 2;
   const long long lo = vec_begin + (long long)rank * per_rank;
   long long hi = lo + per_rank;
@@ -171,7 +188,7 @@ pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n
         st_peer(mine + i + u * stride, v);
       }
   }
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 4u);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 4u, results);
 }
 
 int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
@@ -185,11 +202,11 @@ int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
     uint4* peer = (uint4*)h->peer_grads[1 - h->rank];
     if (h->dtype == DPK_F32)
       pair_allreduce_kernel<float, 4><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->g, peer, vec_begin, n_vec, h->rank,
-                                                                    h->mc_signal, h->local_signal, h->nvls_sig);
+                                                                    h->mc_signal, h->local_signal, h->nvls_sig, h->d_results);
     else
       pair_allreduce_kernel<__nv_bfloat16, 4><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->g, peer, vec_begin, n_vec,
                                                                             h->rank, h->mc_signal, h->local_signal,
-                                                                            h->nvls_sig);
+                                                                            h->nvls_sig, h->d_results);
     DPK_CUDA(cudaGetLastError());
     h->nvls_sig += 4u;
     h->launches++;
@@ -197,7 +214,7 @@ int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
   }
 #define DPK_NVLS_LAUNCH(T, U)                                                                                        \
   nvls_allreduce_kernel<T, U><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->mc_grads, vec_begin, n_vec, h->rank, h->world, \
-                                                            inv_world, h->mc_signal, h->local_signal, h->nvls_sig)
+                                                            inv_world, h->mc_signal, h->local_signal, h->nvls_sig, h->d_results)
   if (h->dtype == DPK_F32) {
     if (unroll == 8) DPK_NVLS_LAUNCH(float, 8); else if (unroll == 2) DPK_NVLS_LAUNCH(float, 2); else DPK_NVLS_LAUNCH(float, 4);
   } else {

@@ -316,6 +316,8 @@ class TrainLoop:
         finally:
             opt.inv_scale = 1.0
             opt.skip_if_nonfinite = False
+        if res[_lib.R_COMM_TIMEOUT]:
+            raise RuntimeError("gradient all-reduce timed out waiting for a peer rank (is a rank down?)")
         if res[_lib.R_SKIPPED]:
             opt.undo_step_count()
             self.lg_loss_scale -= 1
@@ -380,6 +382,8 @@ class TrainLoop:
                 if not block and done >= at_least:
                     break
                 ev.synchronize()
+            if host[_lib.R_COMM_TIMEOUT] != 0:
+                raise RuntimeError("gradient all-reduce timed out waiting for a peer rank (is a rank down?)")
             self.logger.logkv_mean("grad_norm", float(host[_lib.R_LOGGED_NORM]))
             self._norm_inflight.pop(0)
             done += 1

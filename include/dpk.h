@@ -63,6 +63,9 @@ extern "C" {
                                  what TrainLoop._log_grad_norm logs (:265-271)      */
 #define DPK_R_NONFINITE    3  /* 1.0 if any gradient element was inf/nan            */
 #define DPK_R_SKIPPED      4  /* 1.0 if the last fused update predicated itself off */
+#define DPK_R_COMM_TIMEOUT 5  /* set to 1.0 (and left there) if one of the library's own
+                                 all-reduce kernels gave up waiting for a peer rank:
+                                 the gradients of that step are not reduced */
 #define DPK_R_COUNT        8
 
 typedef struct dpk_handle dpk_handle;
