@@ -243,16 +243,15 @@ static int launch_update(dpk_handle* h, const StepScalars& sc, int use_coef, int
   }
 }
 
-static void free_handle(dpk_handle* h) {
-  if (!h) return;
-  if (h->comm) {
-    const NcclApi* api = nccl_api();
-    if (api) api->CommDestroy(h->comm);
-  }
+// Everything ensure_device_state creates; leaves the handle as dpk_create made it.
+static void release_device_state(dpk_handle* h) {
   if (h->comm_stream) cudaStreamDestroy(h->comm_stream);
   if (h->ev_ready) cudaEventDestroy(h->ev_ready);
   if (h->ev_done) cudaEventDestroy(h->ev_done);
   for (cudaEvent_t e : h->ev_bucket_done) cudaEventDestroy(e);
+  h->comm_stream = nullptr;
+  h->ev_ready = h->ev_done = nullptr;
+  h->ev_bucket_done.clear();
   cudaFree(h->d_tiles);
   cudaFree(h->d_seg_tile_begin);
   cudaFree(h->d_partials_pre);
@@ -261,17 +260,41 @@ static void free_handle(dpk_handle* h) {
   cudaFree(h->d_seg_bad);
   cudaFree(h->d_seg_norms);
   cudaFree(h->d_results);
+  h->d_tiles = nullptr; h->d_seg_tile_begin = nullptr;
+  h->d_partials_pre = h->d_partials_post = nullptr;
+  h->d_seg_sumsq = nullptr; h->d_seg_bad = nullptr; h->d_seg_norms = nullptr; h->d_results = nullptr;
   if (h->h_results_pinned) cudaFreeHost(h->h_results_pinned);
-  for (auto& v : h->tev)
+  h->h_results_pinned = nullptr;
+  for (auto& v : h->tev) {
     for (cudaEvent_t e : v) cudaEventDestroy(e);
+    v.clear();
+  }
+  h->tcount[0] = h->tcount[1] = 0;
+}
+
+static void free_handle(dpk_handle* h) {
+  if (!h) return;
+  if (h->comm) {
+    const NcclApi* api = nccl_api();
+    if (api) api->CommDestroy(h->comm);
+  }
+  release_device_state(h);
   delete h;
 }
 
 // Device-side scratch, tables, stream and events: created on the first
 // dpk_bind (dpk_create itself is pure host planning and needs no GPU).
+static int create_device_state(dpk_handle* h);
+
 static int ensure_device_state(dpk_handle* h) {
   if (h->d_results) return 0;
   DPK_GUARD(h);
+  const int rc = create_device_state(h);
+  if (rc) release_device_state(h);  // a failed attempt leaves nothing half-built behind
+  return rc;
+}
+
+static int create_device_state(dpk_handle* h) {
   int sm = 0;
   DPK_CUDA(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, h->device));
   h->sm_count = sm;
