@@ -250,6 +250,8 @@ def run_ours(args):
         eng.broadcast_state(0, True)
         if args.allreduce == "nvls":
             try:
+                if not flat.symmetric:
+                    raise RuntimeError(f"symmetric allocation failed: {flat.symmetric_error}")
                 eng.enable_nvls(flat.grads)
             except Exception as exc:  # no NVSwitch multicast on this box: NCCL carries the all-reduce
                 if rank == 0:

@@ -92,10 +92,17 @@ class FlatState:
             return torch.zeros(n, dtype=self.dtype, device=self.device)
 
         self.params = buf()
+        self.symmetric = False
+        self.symmetric_error = None
         if symmetric_grads:
-            import torch.distributed._symmetric_memory as symm_mem
-            self.grads = symm_mem.empty(n, dtype=self.dtype, device=self.device)
-            self.grads.zero_()
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                self.grads = symm_mem.empty(n, dtype=self.dtype, device=self.device)
+                self.grads.zero_()
+                self.symmetric = True
+            except Exception as exc:  # allocator unavailable: ordinary device memory, NCCL carries the all-reduce
+                self.symmetric_error = exc
+                self.grads = buf()
         else:
             self.grads = buf()
         self.exp_avg, self.exp_avg_sq = buf(), buf()

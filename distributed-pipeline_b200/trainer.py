@@ -156,6 +156,8 @@ class TrainLoop:
                 # symmetric memory; NCCL stays the path when the NVSwitch multicast
                 # mapping cannot be set up (and "nvls" was not demanded)
                 try:
+                    if not self.opt.flat.symmetric:
+                        raise RuntimeError(f"symmetric allocation failed: {self.opt.flat.symmetric_error}")
                     self.opt.engine.enable_nvls(self.opt.flat.grads)
                 except Exception as exc:
                     if grad_allreduce == "nvls":
