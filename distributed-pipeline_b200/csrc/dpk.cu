@@ -408,7 +408,7 @@ int dpk_create(dpk_handle** out, const dpk_config* cfg) {
     h->seg_len.push_back(len);
     n_tiles_ll += (len + tile_elems - 1) / tile_elems;
   }
-  if (n_tiles_ll > 0x7fffffffLL / 2) {
+  if (n_tiles_ll > (1LL << 28)) {  // tile and chunk indices are 32-bit in the kernels
     set_error("dpk_create: %lld tiles; raise tile_elems", n_tiles_ll);
     delete h;
     return DPK_E_LIMIT;
