@@ -317,7 +317,8 @@ def run_ours(args):
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     fused_bpp = bytes_per_param(dtype, len(rates), -1.0, args.grad_mode)
-    per_step = n_buckets if (world > 1 and not args.no_overlap and clip <= 0) else 1
+    pair_fused = (world == 2 and eng.nvls and not args.no_overlap and clip <= 0 and args.grad_mode == "keep")
+    per_step = 1 if pair_fused else (n_buckets if (world > 1 and not args.no_overlap and clip <= 0) else 1)
     if per_step > 1:  # bucket-granular launches: one "launch" of the roofline = one full pass
         kernel_ms = [sum(kernel_ms[i:i + per_step]) for i in range(0, len(kernel_ms) - per_step + 1, per_step)]
     k_ms = sum(kernel_ms) / len(kernel_ms) if kernel_ms else float("nan")
@@ -396,6 +397,7 @@ def run_ours(args):
                        "allreduce": (("own kernels over symmetric memory (NVLS multimem for W>=4, pair exchange for W=2)"
                                       if eng.nvls else "ncclAllReduce(avg)") if world > 1 else None),
                        "update_overlaps_allreduce": bool(world > 1 and not args.no_overlap),
+                       "one_kernel_allreduce_update": bool(pair_fused),
                        "grad_sigma": sigma},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
             "clocks": clocks.summary(),

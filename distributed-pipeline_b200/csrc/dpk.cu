@@ -190,6 +190,7 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   UpdateArgs<T, K> a;
   a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
   for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
+  a.peer_g = (GM == kGradPair) ? (const T*)h->peer_grads[1 - h->rank] : nullptr;
   a.tiles = h->d_tiles;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
@@ -227,6 +228,7 @@ static int launch_update_gm(dpk_handle* h, const StepScalars& sc, int use_coef, 
   switch (gm) {
     case DPK_GRAD_KEEP: return launch_update_impl<T, K, DPK_GRAD_KEEP>(h, sc, use_coef, skip, tb, te, st);
     case DPK_GRAD_CLIPPED: return launch_update_impl<T, K, DPK_GRAD_CLIPPED>(h, sc, use_coef, skip, tb, te, st);
+    case kGradPair: return launch_update_impl<T, K, kGradPair>(h, sc, use_coef, skip, tb, te, st);
     default: return launch_update_impl<T, K, DPK_GRAD_ZERO>(h, sc, use_coef, skip, tb, te, st);
   }
 }
@@ -691,6 +693,10 @@ int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream
   return dpk_grad_norm_finish(h, max_norm, stream);
 }
 
+static int update_range(dpk_handle* h, int tb, int te, double lr, double weight_decay, int64_t adam_step,
+                        double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
+                        cudaStream_t st);
+
 int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double weight_decay, int64_t adam_step,
                             double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
                             void* stream) {
@@ -701,7 +707,37 @@ int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double wei
   int tb = 0, te = 0;
   if (int rc = bucket_tiles(h, bucket, &tb, &te, "dpk_fused_update_bucket")) return rc;
   DPK_GUARD(h);
+  return update_range(h, tb, te, lr, weight_decay, adam_step, inv_scale, use_clip_coef, skip_if_nonfinite, grad_mode,
+                      (cudaStream_t)stream);
+}
+
+// Two ranks, one pass: every gradient element is read once from this rank's HBM
+// and once from the peer's over NVLink, averaged in registers and consumed by
+// the update on the spot -- the all-reduce (torch DDP's reducer,
+// utils/trainer.py:118-125) and optimize() (:237-244) as ONE kernel, the
+// transfer overlapping the update chunk by chunk.  The gradient buffers are
+// left as they were (local, not averaged).
+int dpk_reduce_update_pair(dpk_handle* h, double lr, double weight_decay, int64_t adam_step, double inv_scale,
+                           void* stream) {
+  if (!h) { set_error("dpk_reduce_update_pair: null handle"); return DPK_E_BADARG; }
+  if (!h->bound || !h->mc_grads || h->world != 2) {
+    set_error("dpk_reduce_update_pair: needs two ranks and dpk_bind_nvls");
+    return DPK_E_STATE;
+  }
+  if (adam_step < 1) { set_error("dpk_reduce_update_pair: adam_step %lld < 1", (long long)adam_step); return DPK_E_BADARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = pair_sync(h, st)) return rc;  // the peer's gradients are complete
+  if (int rc = update_range(h, 0, (int)h->tiles.size(), lr, weight_decay, adam_step, inv_scale, 0, 0, kGradPair, st))
+    return rc;
+  if (int rc = pair_sync(h, st)) return rc;  // the peer is done reading ours
+  return dpk_fused_update_finish(h, 0, stream);
+}
+
+static int update_range(dpk_handle* h, int tb, int te, double lr, double weight_decay, int64_t adam_step,
+                        double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
+                        cudaStream_t st) {
 
   // Python-double arithmetic of torch's _multi_tensor_adam (optim/adam.py:770-781),
   // each value then narrowed to fp32 as a kernel argument.

@@ -54,6 +54,7 @@ struct Bucket;
 struct dpk_handle;
 namespace dpk {
 int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st);
+int pair_sync(dpk_handle* h, cudaStream_t st);
 
 struct Bucket {
   int seg_begin, seg_end;     // tensors [seg_begin, seg_end)
@@ -115,6 +116,8 @@ struct dpk_handle {
   unsigned* mc_signal = nullptr;
   const unsigned* local_signal = nullptr;
   int nvls_blocks = 0;
+  int nvls_slots = 0;
+  unsigned pair_sig = 0;  // value of the last slot's counter after the pair barriers enqueued so far
   int nvls_unroll = 4;
   unsigned nvls_sig = 0;  // value of every block counter after the launches enqueued so far
 

@@ -442,6 +442,30 @@ finalize_logged_kernel(const double* __restrict__ seg_sumsq, int n_seg, int skip
 // Reads g,p,m,v and K EMA copies, writes p,m,v and K EMA copies: (7+2K)*s
 // bytes per parameter (+s if the gradient is rewritten or zeroed).
 
+// Internal gradient mode of the two-rank fused pass: the gradient is the average
+// of this rank's and the peer's copy, taken in registers; nothing is written back.
+constexpr int kGradPair = 3;
+
+__device__ __forceinline__ uint4 ld_sys(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+
+// (a+b)/2 per element, one rounding to the state dtype: ncclAvg's / DDP's result for two ranks
+template <typename T>
+__device__ __forceinline__ uint4 average2(const uint4& a, const uint4& b) {
+  using Tr = ElemTraits<T>;
+  float x[Tr::VE], y[Tr::VE];
+  Tr::unpack(a, x);
+  Tr::unpack(b, y);
+#pragma unroll
+  for (int j = 0; j < Tr::VE; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);
+  Tr::rndv(x);
+  return Tr::pack(x);
+}
+
 template <typename T, int K>
 struct UpdateArgs {
   T* p;
@@ -449,6 +473,7 @@ struct UpdateArgs {
   T* m;
   T* v;
   T* ema[K > 0 ? K : 1];
+  const T* peer_g;           // kGradPair only: the other rank's gradient buffer (peer mapping)
   const Tile* tiles;
   int tile_begin, tile_end;  // this launch covers tiles [tile_begin, tile_end)
   int chunk_elems;           // elements per work item: one 16-byte vector per thread
@@ -470,13 +495,17 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
   uint4* vv = reinterpret_cast<uint4*>(a.v) + vidx;
 
   // all loads of this vector are issued before any arithmetic
-  const uint4 rg = (GM == DPK_GRAD_KEEP) ? ld_readonly(gv) : ld_stream(gv);
+  uint4 rg = (GM == DPK_GRAD_KEEP || GM == kGradPair) ? ld_readonly(gv) : ld_stream(gv);
+  uint4 rpeer = make_uint4(0, 0, 0, 0);
+  if (GM == kGradPair) rpeer = ld_sys(reinterpret_cast<const uint4*>(a.peer_g) + vidx);  // over NVLink
   const uint4 rp = ld_stream(pv);
   const uint4 rm = ld_stream(mv);
   const uint4 rv = ld_stream(vv);
   uint4 re[K > 0 ? K : 1];
 #pragma unroll
   for (int k = 0; k < K; ++k) re[k] = ld_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx);
+
+  if (GM == kGradPair) rg = average2<T>(rg, rpeer);  // the all-reduce, without a pass of its own
 
   // outputs start as the inputs so that lanes past a ragged end keep their bytes
   uint4 wg = rg, wp = rp, wm = rm, wv = rv;
@@ -563,7 +592,7 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
     Tr::pack4(wp, c, p);
     Tr::pack4(wm, c, m);
     Tr::pack4(wv, c, v);
-    if (GM != DPK_GRAD_KEEP) Tr::pack4(wg, c, g);
+    if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) Tr::pack4(wg, c, g);
 
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -590,7 +619,7 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
   st_stream(pv, wp);
   st_stream(mv, wm);
   st_stream(vv, wv);
-  if (GM != DPK_GRAD_KEEP) st_stream(gv, wg);
+  if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) st_stream(gv, wg);
 #pragma unroll
   for (int k = 0; k < K; ++k) st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, we[k]);
 }

@@ -139,18 +139,6 @@ nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int
 // reads the peer's copy of its half over NVLink, adds its own, averages, and
 // writes the result into both copies: S/2 in each direction per phase, and the
 // arithmetic is one correctly rounded (a+b)/2 -- bit-identical to ncclAvg.
-template <typename T>
-__device__ __forceinline__ uint4 average2(const uint4& a, const uint4& b) {
-  using Tr = ElemTraits<T>;
-  float x[Tr::VE], y[Tr::VE];
-  Tr::unpack(a, x);
-  Tr::unpack(b, y);
-#pragma unroll
-  for (int j = 0; j < Tr::VE; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);
-  Tr::rndv(x);
-  return Tr::pack(x);
-}
-
 __device__ __forceinline__ uint4 ld_peer(const uint4* p) {
   uint4 r;
   asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -189,6 +177,32 @@ pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n
       }
   }
   block_barrier_all_ranks(mc_sig, local_sig, sig_base + 4u, results);
+}
+
+// A barrier between the two ranks as a kernel of its own: stream order then keeps
+// the big kernel between two of them free of any waiting.  It owns the last
+// signal slot, which no all-reduce block ever touches.
+__global__ void pair_sync_kernel(unsigned* mc_sig, const unsigned* local_sig, int slot, unsigned target, double* results) {
+  __threadfence_system();
+  if (threadIdx.x == 0) {
+    mc_signal_add(mc_sig + slot);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(local_sig + slot) - target) < 0) {
+      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > kPeerTimeoutNs) {
+        results[DPK_R_COMM_TIMEOUT] = 1.0;
+        break;
+      }
+    }
+  }
+}
+
+int pair_sync(dpk_handle* h, cudaStream_t st) {
+  h->pair_sig += 2u;
+  pair_sync_kernel<<<1, 32, 0, st>>>(h->mc_signal, h->local_signal, h->nvls_slots - 1, h->pair_sig, h->d_results);
+  DPK_CUDA(cudaGetLastError());
+  h->launches++;
+  return 0;
 }
 
 int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
@@ -260,9 +274,12 @@ extern "C" int dpk_bind_nvls(dpk_handle* h, void* mc_grads, void* const* peer_gr
   h->mc_grads = mc_grads;
   h->mc_signal = (unsigned*)mc_signal;
   h->local_signal = (const unsigned*)local_signal;
-  h->nvls_blocks = std::min<int>(n_slots, 32);  // link-bound: 32 blocks x 512 threads x 4 vectors saturate NVLink (measured)
+  if (n_slots < 2) { set_error("dpk_bind_nvls: at least 2 signal slots"); return DPK_E_BADARG; }
+  h->nvls_slots = n_slots;
+  h->pair_sig = 0;
+  h->nvls_blocks = std::min<int>(n_slots - 1, 32);  // link-bound: 32 blocks x 512 threads x 4 vectors saturate NVLink (measured)
   h->nvls_unroll = 4;
-  if (const char* e = getenv("DPK_NVLS_BLOCKS")) h->nvls_blocks = std::max(1, std::min<int>(n_slots, atoi(e)));  // tuning
+  if (const char* e = getenv("DPK_NVLS_BLOCKS")) h->nvls_blocks = std::max(1, std::min<int>(n_slots - 1, atoi(e)));  // tuning
   if (const char* e = getenv("DPK_NVLS_UNROLL")) h->nvls_unroll = atoi(e);
   h->nvls_sig = 0;
   return 0;

@@ -190,6 +190,11 @@ class Engine:
         _lib.check(self.lib.dpk_fused_update_finish(self._h, int(skip_if_nonfinite),
                                                     _stream_ptr(stream, self.device)))
 
+    def reduce_update_pair(self, lr: float, weight_decay: float, adam_step: int, inv_scale: float = 1.0, stream=None):
+        """Two ranks: all-reduce and update as one kernel (see dpk_reduce_update_pair)."""
+        _lib.check(self.lib.dpk_reduce_update_pair(self._h, lr, weight_decay, adam_step, inv_scale,
+                                                   _stream_ptr(stream, self.device)))
+
     @property
     def results(self) -> torch.Tensor:
         """Device tensor (float64[R_COUNT]) aliasing the library's result block."""

@@ -77,6 +77,14 @@ class FusedAdamW:
         eng = self.engine
         g = self.param_groups[0]
         n = len(eng.buckets)
+        if (eng.world_size == 2 and eng.nvls and max_norm <= 0 and self.grad_mode == _lib.GRAD_KEEP
+                and not self.skip_if_nonfinite):
+            # two ranks, gradients not needed afterwards: exchange and update in ONE kernel
+            self.step_count += 1
+            eng.reduce_update_pair(float(g["lr"]), float(g["weight_decay"]), self.step_count, self.inv_scale)
+            self._clip_pending = False
+            self.ema_done = [True] * len(self.ema_rates)
+            return
         if eng.world_size > 1:
             for b in range(n):
                 eng.bucket_ready(b)

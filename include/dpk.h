@@ -215,6 +215,18 @@ int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stre
 #define DPK_OPT_NORM_STAGING 2
 int dpk_set_option(dpk_handle* h, int32_t option, int64_t value);
 
+/* Two ranks only (after dpk_bind_nvls): gradient all-reduce AND the fused update
+ * as one kernel.  Each gradient element is read from this rank's buffer and, over
+ * NVLink, from the peer's, averaged in registers ((a+b)/2, one rounding: what
+ * ncclAvg / DDP give) and consumed by AdamW + EMA on the spot, so the exchange
+ * overlaps the update chunk by chunk and the averaged gradient never travels
+ * through HBM.  Replaces dpk_bucket_ready (all buckets) + dpk_wait_allreduce +
+ * dpk_fused_update(grad_mode KEEP, no clip) with identical state afterwards; the
+ * gradient buffers themselves stay local (not averaged).  DPK_R_LOGGED_NORM is
+ * the norm of the averaged gradient. */
+int dpk_reduce_update_pair(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
+                           double inv_scale, void* stream);
+
 /* Device address of the result block (DPK_R_COUNT doubles). */
 int dpk_result_ptr(dpk_handle* h, void** d_out);
 /* Copy the result block to `out[DPK_R_COUNT]` and wait for it: the single host

@@ -117,6 +117,43 @@ def main():
         loop._reducer.remove()
         del loop, ddp
 
+    # ---- two ranks: all-reduce + update as ONE kernel == all-reduce, then update ----------
+    if world == 2:
+        from distributed_pipeline_b200 import FusedAdamW, _lib
+        for dtype in (torch.float32, torch.bfloat16):
+            shapes = [(1000, 33), (7,), (300000,), (128, 128), (5,), (200003,)]
+
+            def make():
+                torch.manual_seed(7)
+                ps = [torch.nn.Parameter((torch.randn(s, device=dev) * 0.02).to(dtype)) for s in shapes]
+                o = FusedAdamW(ps, lr=1e-3, weight_decay=0.01, ema_rates=[0.999, 0.9], bucket_cap_mb=0.5,
+                               grad_mode=_lib.GRAD_KEEP, symmetric_grads=True)
+                o.engine.init_comm()
+                o.engine.enable_nvls(o.flat.grads)
+                return o
+            fused, staged = make(), make()
+            gen = torch.Generator(device=dev).manual_seed(50 + rank)
+            for it in range(3):
+                g = (torch.randn(fused.flat.layout.n_elems, device=dev, generator=gen) * 0.05).to(dtype)
+                fused.flat.grads.copy_(g)
+                staged.flat.grads.copy_(g)
+                fused.reduce_and_step()                       # dpk_reduce_update_pair
+                for b in range(len(staged.engine.buckets)):   # all-reduce every bucket, then one update
+                    staged.engine.bucket_ready(b)
+                staged.engine.wait_allreduce()
+                staged.step()
+                torch.cuda.synchronize()
+                assert torch.equal(fused.flat.grads, g), "the fused pass leaves the local gradient untouched"
+                for a, b in ((fused.flat.params, staged.flat.params), (fused.flat.exp_avg, staged.flat.exp_avg),
+                             (fused.flat.exp_avg_sq, staged.flat.exp_avg_sq), (fused.flat.emas[0], staged.flat.emas[0]),
+                             (fused.flat.emas[1], staged.flat.emas[1])):
+                    assert torch.equal(a, b), f"{dtype}: one-kernel pair update differs from all-reduce + update"
+                ra, rb = fused.engine.read_results_sync(), staged.engine.read_results_sync()
+                assert ra[_lib.R_LOGGED_NORM] == rb[_lib.R_LOGGED_NORM] and ra[_lib.R_COMM_TIMEOUT] == 0
+            if rank == 0:
+                print(f"{dtype}: one-kernel pair all-reduce+update bit-identical to all-reduce then update", flush=True)
+            del fused, staged
+
     # ---- loss-aware sampler: one packed all-gather, rank-major order -------------------
     T = 50
     eng_loop = Loop(model=SyntheticDiffuSeq(**TOY).to(dev), data=iter(data), batch_size=8, microbatch=4, lr=1e-3,
