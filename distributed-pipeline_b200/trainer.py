@@ -165,9 +165,17 @@ class TrainLoop:
                     self.logger.log(f"symmetric-memory all-reduce unavailable ({exc}); using NCCL")
             self._reducer = BucketReducer(self.opt.flat, self.opt.engine)
             self.ddp_model = FlatDDP(self.model, self._reducer)
+            # Two ranks, nobody needs the averaged gradient afterwards, no clipping: the
+            # exchange moves out of backward and into the update kernel itself
+            # (dpk_reduce_update_pair); .grad then keeps this rank's local gradient.
+            self._pair_fused = (self.opt.engine.nvls and world == 2 and grads_after_step == "keep"
+                                and not self.use_fp16 and not self.gradient_clipping > 0)
+            if self._pair_fused:
+                self._reducer.enabled = False
         else:
             self.use_ddp = False
             self._reducer = None
+            self._pair_fused = False
             self.ddp_model = self.model
 
         self._in_optimize = False
@@ -287,13 +295,19 @@ class TrainLoop:
         self._drain_norms(block=False)
         if self.use_fp16:
             return self._optimize_fp16()
+        if self._pair_fused and self.gradient_clipping > 0:
+            raise RuntimeError("gradient_clipping was switched on after construction: this loop exchanges gradients "
+                               "inside the update kernel (grads_after_step='keep', 2 ranks); build it with clipping set")
         self._in_optimize = True
         try:
             if self.gradient_clipping > 0:
                 self.grad_clip()
             self._log_grad_norm()
             self._anneal_lr()
-            self.opt.step()
+            if self._pair_fused and not self.gradient_clipping > 0:
+                self.opt.reduce_and_step()   # all-reduce + AdamW + EMA, one kernel
+            else:
+                self.opt.step()
             for rate, params in zip(self.ema_rate, self.ema_params):
                 update_ema(params, self.master_params, rate=rate)
         finally:

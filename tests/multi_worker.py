@@ -50,7 +50,8 @@ def main():
     logger.configure(dir=os.path.join(tmp, f"log{rank}"))
     data = batches(1234 + rank, 8, 6)
 
-    for clip, allreduce in ((-1.0, "nvls"), (1.0, "nvls"), (1.0, "nccl")):
+    for clip, allreduce, after in ((-1.0, "nvls", "clipped"), (1.0, "nvls", "clipped"), (1.0, "nccl", "clipped"),
+                                   (-1.0, "nvls", "keep")):
         torch.manual_seed(102 + rank)              # ranks start DIFFERENT: rank 0's parameters must win
         model = SyntheticDiffuSeq(**TOY).to(dev)
         torch.manual_seed(102 + rank)
@@ -58,8 +59,10 @@ def main():
 
         loop = Loop(model=model, data=iter(data), batch_size=8, microbatch=4, lr=1e-3, ema_rate="0.9999,0.999",
                     log_interval=10 ** 9, save_interval=10 ** 9, resume_checkpoint="", weight_decay=0.01,
-                    learning_steps=100, checkpoint_path=tmp, gradient_clipping=clip, grad_allreduce=allreduce)
+                    learning_steps=100, checkpoint_path=tmp, gradient_clipping=clip, grad_allreduce=allreduce,
+                    grads_after_step=after)
         assert loop.opt.engine.nvls == (allreduce == "nvls")
+        assert loop._pair_fused == (world == 2 and after == "keep" and clip <= 0)
         assert loop.use_ddp and loop.global_batch == 8 * world
         assert loop.opt.engine.world_size == world
 
@@ -111,7 +114,7 @@ def main():
         dist.broadcast(flat, 0)
         assert torch.equal(flat, loop.opt.flat.params)
         if rank == 0:
-            print(f"clip={clip} allreduce={allreduce}: {nbit}/{len(port.params)} parameter tensors bit-identical to "
+            print(f"clip={clip} allreduce={allreduce} grads_after_step={after}: {nbit}/{len(port.params)} parameter tensors bit-identical to "
                   f"DDP+AdamW after 6 steps",
                   flush=True)
         loop._reducer.remove()
