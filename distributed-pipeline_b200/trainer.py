@@ -227,24 +227,32 @@ class TrainLoop:
             self.opt.load_state_dict(dist_util.load_state_dict(opt_checkpoint, map_location=dist_util.dev()))
 
     # ---- the loop (reference :175-201) ---------------------------------------
+    def _steps_remain(self):
+        return not self.learning_steps or self.step + self.resume_step < self.learning_steps
+
+    def _periodic_work(self):
+        """What the reference does between steps (utils/trainer.py:182-193), in its order:
+        dump the logger, evaluate, checkpoint."""
+        if self.step % self.log_interval == 0:
+            self.flush_logs()
+            self.logger.dumpkvs()
+        if self.eval_data is not None and self.step % self.eval_interval == 0:
+            self.forward_only(next(self.eval_data))
+            print('eval on validation set')
+            self.logger.dumpkvs()
+            if dist_util.get_rank() == 0:
+                for callback in self.eval_callbacks:
+                    callback(self)
+        if self.step > 0 and self.step % self.save_interval == 0:
+            self.save()
+
     def run_loop(self):
-        while not self.learning_steps or self.step + self.resume_step < self.learning_steps:
-            batch = next(self.data)
-            self.run_step(batch)
-            if self.step % self.log_interval == 0:
-                self.flush_logs()
-                self.logger.dumpkvs()
-            if self.eval_data is not None and self.step % self.eval_interval == 0:
-                self.forward_only(next(self.eval_data))
-                print('eval on validation set')
-                self.logger.dumpkvs()
-                if dist_util.get_rank() == 0:
-                    for callback in self.eval_callbacks:
-                        callback(self)
-            if self.step > 0 and self.step % self.save_interval == 0:
-                self.save()
+        while self._steps_remain():
+            self.run_step(next(self.data))
+            self._periodic_work()
             self.step += 1
-        if (self.step - 1) % self.save_interval != 0:
+        last_done = self.step - 1
+        if last_done % self.save_interval != 0:   # not already saved by the loop
             self.save()
 
     __call__ = run_loop
@@ -272,18 +280,22 @@ class TrainLoop:
         with self.ddp_model.no_sync():
             return self.compute_losses(micro_batch)
 
+    def _microbatch_losses(self, batch):
+        """_zero_grad, then the losses of every microbatch in turn, each logged the way the
+        reference logs it -- with mode="eval" even while training (sic, :234)."""
+        self._zero_grad()
+        for start in range(0, self.get_batch_length(batch), self.microbatch):
+            losses = self._common_forward(batch, start)
+            self.log_loss_dict(mode="eval", losses=losses)
+            yield losses
+
     @torch.no_grad()
     def forward_only(self, batch):
-        self._zero_grad()
-        for i in range(0, self.get_batch_length(batch), self.microbatch):
-            losses = self._common_forward(batch, i)
-            self.log_loss_dict(mode="eval", losses=losses)
+        for _ in self._microbatch_losses(batch):
+            pass
 
     def forward_backward(self, batch):
-        self._zero_grad()
-        for i in range(0, self.get_batch_length(batch), self.microbatch):
-            losses = self._common_forward(batch, i)
-            self.log_loss_dict(mode="eval", losses=losses)  # sic: the reference logs "eval" here (:234)
+        for losses in self._microbatch_losses(batch):
             if self.use_fp16:
                 scale = 2.0 ** self.lg_loss_scale
                 losses = {k: v * scale for k, v in losses.items()}
@@ -347,20 +359,20 @@ class TrainLoop:
             self._grads_are_zero = True
 
     def grad_clip(self):
-        max_grad_norm = self.gradient_clipping
-        if hasattr(self.opt, "clip_grad_norm"):
-            # the reference's own seam for optimizers that clip themselves (:248-250)
-            self.opt.clip_grad_norm(max_grad_norm)
+        # the reference's own seam for optimizers that clip themselves (:248-250);
+        # FusedAdamW does: pass 1 runs, the coefficient stays on the device
+        clip_own = getattr(self.opt, "clip_grad_norm", None)
+        if clip_own is not None:
+            clip_own(self.gradient_clipping)
         else:
-            torch.nn.utils.clip_grad_norm_(self.model.parameters(), max_grad_norm)
+            torch.nn.utils.clip_grad_norm_(self.model.parameters(), self.gradient_clipping)
 
     def _anneal_lr(self):
-        if not self.learning_steps:
-            return
-        frac_done = (self.step + self.resume_step) / self.learning_steps
-        lr = self.lr * (1 - frac_done)
-        for param_group in self.opt.param_groups:
-            param_group["lr"] = lr
+        """Linear decay to zero over learning_steps, from TrainLoop's own step counter (:257-263)."""
+        if self.learning_steps:
+            frac_done = (self.step + self.resume_step) / self.learning_steps
+            for group in self.opt.param_groups:
+                group["lr"] = self.lr * (1 - frac_done)
 
     def _log_grad_norm(self):
         """Reference :265-271 reads 209 sums back one by one.  Inside optimize()
@@ -413,32 +425,34 @@ class TrainLoop:
         self.logger.logkv("samples", (self.step + self.resume_step + 1) * self.global_batch)
 
     # ---- checkpoints (reference :277-355): same file names and layouts ---------
+    def _checkpoint_file(self, stem):
+        return os.path.join(self.checkpoint_path, f"{stem}_{(self.step + self.resume_step):06d}.pt")
+
     def save(self):
         self.flush_logs()
-        self._save_checkpoint(0, self.master_params)
-        for r, p in zip(self.ema_rate, self.ema_params):
-            self._save_checkpoint(r, p)
+        for rate, params in [(0, self.master_params), *zip(self.ema_rate, self.ema_params)]:
+            self._save_checkpoint(rate, params)
         self._save_opt()
         dist_util.barrier()
 
     def _save_checkpoint(self, rate, params):
-        state_dict = self._master_params_to_state_dict(params)
-        if dist_util.get_rank() == 0:
-            self.logger.log(f"saving model {rate}...")
-            n = self.step + self.resume_step
-            filename = f"model_{n:06d}.pt" if not rate else f"ema_{rate}_{n:06d}.pt"
-            path = os.path.join(self.checkpoint_path, filename)
-            print('writing to', path)
-            with open(path, "wb") as f:
-                torch.save(state_dict, f)
+        state_dict = self._master_params_to_state_dict(params)   # on every rank, like the reference
+        if dist_util.get_rank() != 0:
+            return
+        self.logger.log(f"saving model {rate}...")
+        path = self._checkpoint_file(f"ema_{rate}" if rate else "model")
+        print('writing to', path)
+        with open(path, "wb") as f:
+            torch.save(state_dict, f)
 
     def _save_opt(self):
-        if dist_util.get_rank() == 0:
-            self.logger.log("saving optimizer...")
-            path = os.path.join(self.checkpoint_path, f"opt_{(self.step + self.resume_step):06d}.pt")
-            print('writing to', path)
-            with open(path, "wb") as f:
-                torch.save(self.opt.state_dict(), f)
+        if dist_util.get_rank() != 0:
+            return
+        self.logger.log("saving optimizer...")
+        path = self._checkpoint_file("opt")
+        print('writing to', path)
+        with open(path, "wb") as f:
+            torch.save(self.opt.state_dict(), f)
 
     def _master_params_to_state_dict(self, master_params, key=None):
         state_dict = self.model.state_dict()
