@@ -302,7 +302,9 @@ int dpk_sampler_create(dpk_sampler** out, int32_t device, int32_t n_timesteps,
 int dpk_sampler_destroy(dpk_sampler* s);
 /* Gather every rank's (timestep, loss) records (rank-major, batch order) over
  * the handle's communicator (h may be NULL or single-rank: local only) and
- * apply update_with_all_losses.  d_ts int64[n_local], d_losses float[n_local]. */
+ * apply update_with_all_losses.  d_ts int64[n_local], d_losses float[n_local].
+ * Asynchronous, except that the first call (and the first one with a larger
+ * communicator) synchronises `stream` once to size the gather buffer. */
 int dpk_sampler_update(dpk_sampler* s, dpk_handle* h, const int64_t* d_ts,
                        const float* d_losses, int32_t n_local, void* stream);
 /* weights() into a device array of n_timesteps doubles. */
