@@ -3,6 +3,7 @@
 ``oracle/dpk_oracle.c``   scalar C restatement of the reference's arithmetic
 ``oracle/torch_port.py``  the same path spelled with the torch ops the reference
                           calls (CPU baseline for bench.py; tight oracle on GPU)
+``oracle/truth_fp64.py``  the same recurrence in float64 numpy (no rounding points): tier T0
 ``oracle/sampler_oracle.py``  numpy restatement of the upstream loss-aware sampler
 ``oracle/make_golden.py`` runs the *real* reference TrainLoop (from
                           /root/reference, only in the build container) and

@@ -131,3 +131,33 @@ def test_c_oracle_bf16_matches_torch_cpu_bf16_rounding_points():
                           flavour=oracle.CPU)
     assert np.array_equal(mo, m.view(torch.int16).numpy().view(np.uint16))
     assert np.array_equal(vo, v.view(torch.int16).numpy().view(np.uint16))
+
+
+def test_c_oracle_tracks_the_float64_truth():
+    """T0: the fp32 restatement stays within fp32 rounding of the same recurrence carried in float64."""
+    from oracle import truth_fp64
+    rng = np.random.RandomState(3)
+    n, steps = 30000, 20
+    p32 = (rng.randn(n) * 0.02).astype(np.float32)
+    m32, v32, e32 = np.zeros(n, np.float32), np.zeros(n, np.float32), p32.copy()
+    p64, m64, v64, e64 = (a.astype(np.float64) for a in (p32, m32, v32, e32))
+    for t in range(1, steps + 1):
+        g = (rng.randn(n) * 0.05).astype(np.float32)
+        r = oracle.grad_norm(oracle.F32, g, [0], [n], 1.0, 1.0)
+        nrm, coef = truth_fp64.step(p64, g.astype(np.float64), m64, v64, [e64], [0.999], 1e-3, 0.01, t, max_norm=1.0)
+        assert abs(r["total"] - nrm) <= 1e-6 * nrm and abs(r["coef"] - coef) <= 1e-6 * coef
+        oracle.adamw_ema_step(oracle.F32, p32, g.copy(), m32, v32, [e32], [0.999], 1e-3, 0.01, t, coef=r["coef"])
+    for a32, a64 in ((p32, p64), (m32, m64), (v32, v64), (e32, e64)):
+        assert _close(a32, a64, rtol=2e-6).all()
+
+
+def test_uniform_sampler_draws_like_upstream():
+    from distributed_pipeline_b200.sampler import UniformSampler, create_named_schedule_sampler
+    s = create_named_schedule_sampler("uniform", 2000)
+    assert isinstance(s, UniformSampler)
+    np.random.seed(11)
+    idx, w = s.sample(64, "cpu")
+    np.random.seed(11)
+    want = np.random.choice(2000, size=(64,), p=np.ones(2000) / 2000)
+    assert np.array_equal(idx.numpy(), want) and idx.dtype == torch.int64
+    assert torch.equal(w, torch.ones(64)) and w.dtype == torch.float32
