@@ -8,7 +8,7 @@ surface the reference touches: ``param_groups[i]["lr"]`` (``:262-263``),
 looks for (``:248-250``).  ``step()`` is one kernel launch: unscale, clip,
 AdamW and every EMA rate.
 """
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, Sequence
 
 import torch
 

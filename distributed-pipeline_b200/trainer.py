@@ -19,10 +19,9 @@ foreach AdamW + 2K EMA ops   one fused kernel (pass 2)
 There is no CPU path: constructing a ``TrainLoop`` around a model that is not
 on a CUDA device raises.
 """
-import math
 import os
 import weakref
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
 

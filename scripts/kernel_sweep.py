@@ -1,6 +1,6 @@
 """Times the fused-update and sum-of-squares kernels alone (CUDA events inside
 the library) over dtype x K x grad mode on DiffuSeq-base shapes."""
-import sys, os, json
+import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from distributed_pipeline_b200 import _lib

@@ -3,7 +3,7 @@ Times update_with_local_losses (pack + gather + in-order history update) and wei
 upstream-style host implementation (3 all_gathers + 2*W*B .item() syncs + Python loop) next to it."""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch, torch.distributed as dist
+import torch, torch.distributed as dist
 from distributed_pipeline_b200 import FusedAdamW
 from distributed_pipeline_b200.sampler import LossSecondMomentResampler
 from oracle.sampler_oracle import LossSecondMomentResamplerOracle

@@ -3,7 +3,6 @@ import numpy as np
 import torch
 
 import oracle
-from distributed_pipeline_b200 import _lib
 from distributed_pipeline_b200.engine import Engine
 from distributed_pipeline_b200.flat import FlatLayout
 

@@ -1,7 +1,6 @@
 """Worker for tests/test_gpu_multi.py: one rank of an NCCL job on real GPUs.
 Compares the drop-in TrainLoop (flat NCCL buckets + fused update) with the
 reference's loop restated on torch DDP + torch.optim.AdamW + eager EMA."""
-import copy
 import os
 import sys
 

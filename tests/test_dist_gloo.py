@@ -10,7 +10,6 @@ that performs the bucket all-reduce with gloo on the flat CPU gradient buffer.
 import os
 import sys
 
-import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp

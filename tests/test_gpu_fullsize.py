@@ -8,7 +8,7 @@ import torch
 import oracle
 from distributed_pipeline_b200 import _lib
 from distributed_pipeline_b200.synthetic import diffuseq_shapes, numel
-from helpers import FlatProblem, assert_bits_equal, rel_err, to_np
+from helpers import FlatProblem, assert_bits_equal, rel_err
 from oracle.torch_port import ReferenceUpdatePort
 
 pytestmark = pytest.mark.gpu

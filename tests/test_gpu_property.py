@@ -1,13 +1,12 @@
 """Property test: random layouts (empty, 1-element, ragged, tile-straddling tensors), dtypes, EMA counts, gradient
 modes, decay, loss scale and clipping -- the fused path must land on the C oracle's bits every time."""
-import numpy as np
 import pytest
 import torch
 from hypothesis import HealthCheck, given, settings, strategies as st
 
 import oracle
 from distributed_pipeline_b200 import _lib
-from helpers import FlatProblem, assert_bits_equal, rel_err, to_np
+from helpers import FlatProblem, assert_bits_equal, to_np
 
 pytestmark = pytest.mark.gpu
 

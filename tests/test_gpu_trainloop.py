@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 import torch
 
-from distributed_pipeline_b200 import TrainLoop, logger, update_ema, _lib
+from distributed_pipeline_b200 import TrainLoop, logger, update_ema
 from distributed_pipeline_b200.synthetic import SyntheticDiffuSeq
 from oracle.torch_port import ReferenceUpdatePort
 

@@ -4,7 +4,6 @@ given the same clip coefficient; the norm itself to the 1e-5 `north_star` states
 """
 import math
 
-import numpy as np
 import pytest
 import torch
 

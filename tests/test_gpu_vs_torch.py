@@ -10,7 +10,7 @@ import pytest
 import torch
 
 from distributed_pipeline_b200 import _lib
-from helpers import FlatProblem, rel_err, to_np
+from helpers import FlatProblem, rel_err
 from oracle.torch_port import ReferenceUpdatePort
 
 pytestmark = pytest.mark.gpu

@@ -1,7 +1,6 @@
 """Host-side logic that needs neither a GPU nor a process group."""
 import inspect
 
-import numpy as np
 import pytest
 import torch
 

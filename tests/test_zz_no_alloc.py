@@ -15,8 +15,6 @@ tests use -- and oversize input is refused with DPK_E_LIMIT.
 Collected last on purpose (file name): a run that stops at the first failure has
 then already run every other test.
 """
-import ctypes as C
-
 import pytest
 import torch
 
