@@ -69,6 +69,7 @@ SIGNATURES = {
     "dpk_num_buckets": (C.c_int, [_VP]),
     "dpk_bucket_range": (C.c_int, [_VP, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "dpk_bucket_ready": (C.c_int, [_VP, C.c_int32, _VP]),
+    "dpk_all_buckets_ready": (C.c_int, [_VP, _VP]),
     "dpk_wait_bucket": (C.c_int, [_VP, C.c_int32, _VP]),
     "dpk_wait_allreduce": (C.c_int, [_VP, _VP]),
     "dpk_broadcast_state": (C.c_int, [_VP, C.c_int32, C.c_int32, _VP]),

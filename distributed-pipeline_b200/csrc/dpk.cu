@@ -560,20 +560,19 @@ int dpk_bucket_range(const dpk_handle* h, int32_t b, int64_t* start, int64_t* co
   return 0;
 }
 
-int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream) {
-  if (!h || b < 0 || b >= (int)h->buckets.size()) { set_error("dpk_bucket_ready: bad bucket"); return DPK_E_BADARG; }
-  if (!h->bound) { set_error("dpk_bucket_ready: buffers not bound"); return DPK_E_STATE; }
-  std::lock_guard<std::mutex> lock(h->mu);
-  DPK_GUARD(h);
-  if (h->world <= 1) return 0;  // single replica: nothing to exchange
+// Caller holds h->mu.  `chained`: a previous bucket of the same chain has already
+// made sure every rank's gradients are complete (see dpk_all_buckets_ready).
+static int enqueue_bucket(dpk_handle* h, int b, cudaStream_t producer, bool chained) {
   const NcclApi* api = nccl_api();
   if (!api || !h->comm) { set_error("dpk_bucket_ready: communicator not initialised"); return DPK_E_STATE; }
   const Bucket& bk = h->buckets[b];
-  DPK_CUDA(cudaEventRecord(h->ev_ready, (cudaStream_t)producer_stream));
-  DPK_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_ready, 0));
+  if (!chained) {
+    DPK_CUDA(cudaEventRecord(h->ev_ready, producer));
+    DPK_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_ready, 0));
+  }
   if (h->mc_grads) {
-    // our own switch-reduced all-reduce on the multicast mapping (dpk_nvls.cu)
-    if (int rc = nvls_allreduce(h, bk, h->comm_stream)) return rc;
+    // our own all-reduce over symmetric memory (dpk_nvls.cu)
+    if (int rc = nvls_allreduce(h, bk, !chained, h->comm_stream)) return rc;
   } else {
     char* base = (char*)h->g + bk.start * elem_size(h->dtype);
     // ncclAvg pre-multiplies each rank's contribution by 1/W and sums: the
@@ -585,6 +584,26 @@ int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream) {
   DPK_CUDA(cudaEventRecord(h->ev_done, h->comm_stream));
   h->bucket_pending[b] = 1;
   h->any_enqueued = true;
+  return 0;
+}
+
+int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream) {
+  if (!h || b < 0 || b >= (int)h->buckets.size()) { set_error("dpk_bucket_ready: bad bucket"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_bucket_ready: buffers not bound"); return DPK_E_STATE; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  if (h->world <= 1) return 0;  // single replica: nothing to exchange
+  return enqueue_bucket(h, b, (cudaStream_t)producer_stream, false);
+}
+
+int dpk_all_buckets_ready(dpk_handle* h, void* producer_stream) {
+  if (!h) { set_error("dpk_all_buckets_ready: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_all_buckets_ready: buffers not bound"); return DPK_E_STATE; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  if (h->world <= 1) return 0;
+  for (int b = 0; b < (int)h->buckets.size(); ++b)
+    if (int rc = enqueue_bucket(h, b, (cudaStream_t)producer_stream, b > 0)) return rc;
   return 0;
 }
 

@@ -53,7 +53,7 @@ struct Bucket;
 }  // namespace dpk
 struct dpk_handle;
 namespace dpk {
-int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st);
+int nvls_allreduce(dpk_handle* h, const Bucket& bk, bool start_barrier, cudaStream_t st);
 int pair_sync(dpk_handle* h, cudaStream_t st);
 
 struct Bucket {

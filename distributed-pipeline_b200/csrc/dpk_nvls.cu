@@ -111,9 +111,14 @@ __device__ __forceinline__ void multimem_st(uint4* mc, const uint4& v) {
 template <typename T, int kNvlsUnroll>
 __global__ void __launch_bounds__(kNvlsThreads)
 nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int rank, int world, float inv_world,
-                      unsigned* mc_sig, const unsigned* local_sig, unsigned sig_base, double* results) {
+                      unsigned* mc_sig, const unsigned* local_sig, unsigned sig_base, int start_barrier,
+                      double* results) {
   // every rank's local gradients for this range are complete once its block b is here
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results);
+  // (skipped for the later buckets of a chain whose first bucket already established it)
+  if (start_barrier) {
+    block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results);
+    sig_base += (unsigned)world;
+  }
 
   const long long per_rank = (n_vec + world - 1) / world;
   const long long lo = vec_begin + (long long)rank * per_rank;
@@ -131,7 +136,7 @@ nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int
   }
 
   // every rank's slice has been written into every copy once all block-b's are here
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u * (unsigned)world, results);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results);
 }
 
 // Two ranks: the switch has nothing to save (a multicast store also echoes the
@@ -153,8 +158,11 @@ __device__ __forceinline__ void st_peer(uint4* p, const uint4& v) {
 template <typename T, int U>
 __global__ void __launch_bounds__(kNvlsThreads)
 pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n_vec, int rank, unsigned* mc_sig,
-                      const unsigned* local_sig, unsigned sig_base, double* results) {
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results);
+                      const unsigned* local_sig, unsigned sig_base, int start_barrier, double* results) {
+  if (start_barrier) {
+    block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results);
+    sig_base += 2u;
+  }
   const long long per_rank = (n_vec + 1) / 2;
   const long long lo = vec_begin + (long long)rank * per_rank;
   long long hi = lo + per_rank;
@@ -176,7 +184,7 @@ pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n
         st_peer(mine + i + u * stride, v);
       }
   }
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 4u, results);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results);
 }
 
 // A barrier between the two ranks as a kernel of its own: stream order then keeps
@@ -205,7 +213,7 @@ int pair_sync(dpk_handle* h, cudaStream_t st) {
   return 0;
 }
 
-int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
+int nvls_allreduce(dpk_handle* h, const Bucket& bk, bool start_barrier, cudaStream_t st) {
   const int ve = h->dtype == DPK_F32 ? 4 : 8;
   const long long vec_begin = bk.start / ve, n_vec = bk.count / ve;
   const float inv_world = 1.0f / (float)h->world;
@@ -216,19 +224,20 @@ int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
     uint4* peer = (uint4*)h->peer_grads[1 - h->rank];
     if (h->dtype == DPK_F32)
       pair_allreduce_kernel<float, 4><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->g, peer, vec_begin, n_vec, h->rank,
-                                                                    h->mc_signal, h->local_signal, h->nvls_sig, h->d_results);
+                                                                    h->mc_signal, h->local_signal, h->nvls_sig, (int)start_barrier,
+                                                                    h->d_results);
     else
       pair_allreduce_kernel<__nv_bfloat16, 4><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->g, peer, vec_begin, n_vec,
                                                                             h->rank, h->mc_signal, h->local_signal,
-                                                                            h->nvls_sig, h->d_results);
+                                                                            h->nvls_sig, (int)start_barrier, h->d_results);
     DPK_CUDA(cudaGetLastError());
-    h->nvls_sig += 4u;
+    h->nvls_sig += start_barrier ? 4u : 2u;
     h->launches++;
     return 0;
   }
 #define DPK_NVLS_LAUNCH(T, U)                                                                                        \
   nvls_allreduce_kernel<T, U><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->mc_grads, vec_begin, n_vec, h->rank, h->world, \
-                                                            inv_world, h->mc_signal, h->local_signal, h->nvls_sig, h->d_results)
+                                                            inv_world, h->mc_signal, h->local_signal, h->nvls_sig, (int)start_barrier, h->d_results)
   if (h->dtype == DPK_F32) {
     if (unroll == 8) DPK_NVLS_LAUNCH(float, 8); else if (unroll == 2) DPK_NVLS_LAUNCH(float, 2); else DPK_NVLS_LAUNCH(float, 4);
   } else {
@@ -236,7 +245,7 @@ int nvls_allreduce(dpk_handle* h, const Bucket& bk, cudaStream_t st) {
   }
 #undef DPK_NVLS_LAUNCH
   DPK_CUDA(cudaGetLastError());
-  h->nvls_sig += 2u * (unsigned)h->world;  // two barriers per launch, W arrivals each
+  h->nvls_sig += (start_barrier ? 2u : 1u) * (unsigned)h->world;  // W arrivals per barrier
   h->launches++;
   return 0;
 }

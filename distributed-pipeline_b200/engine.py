@@ -150,6 +150,9 @@ class Engine:
     def bucket_ready(self, b: int, stream=None):
         _lib.check(self.lib.dpk_bucket_ready(self._h, b, _stream_ptr(stream, self.device)))
 
+    def all_buckets_ready(self, stream=None):
+        _lib.check(self.lib.dpk_all_buckets_ready(self._h, _stream_ptr(stream, self.device)))
+
     def wait_bucket(self, b: int, stream=None):
         _lib.check(self.lib.dpk_wait_bucket(self._h, b, _stream_ptr(stream, self.device)))
 

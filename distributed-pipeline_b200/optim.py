@@ -85,7 +85,10 @@ class FusedAdamW:
             self._clip_pending = False
             self.ema_done = [True] * len(self.ema_rates)
             return
-        if eng.world_size > 1:
+        if eng.world_size >= 4:
+            # every gradient is already in place: one "peers complete" barrier serves all buckets
+            eng.all_buckets_ready()
+        elif eng.world_size > 1:
             for b in range(n):
                 eng.bucket_ready(b)
         if max_norm > 0:

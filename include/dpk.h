@@ -148,6 +148,12 @@ int dpk_bucket_range(const dpk_handle* h, int32_t b, int64_t* start, int64_t* co
  * its all-reduce on the library's communication stream.  Thread-safe (it is
  * called from autograd's engine thread). */
 int dpk_bucket_ready(dpk_handle* h, int32_t b, void* producer_stream);
+/* Every gradient of every bucket has been produced on `producer_stream` (a
+ * post-backward update with nothing left to overlap): enqueue all buckets in
+ * index order.  Same as dpk_bucket_ready for b = 0..n-1, except that the
+ * library's own all-reduce kernels then need their "all ranks' gradients are
+ * complete" barrier only once, for the first bucket. */
+int dpk_all_buckets_ready(dpk_handle* h, void* producer_stream);
 /* Make `consumer_stream` wait for bucket b's all-reduce only (no-op if none is
  * outstanding): lets the caller consume buckets as they land while later ones
  * are still on the wire. */

@@ -23,7 +23,10 @@ for dtype in (torch.float32, torch.bfloat16):
         flat.grads.copy_(g)
         if it == 0 and not eng.nvls:
             eng.enable_nvls(flat.grads)
-        for b in range(nb): eng.bucket_ready(b)
+        if it == 2:
+            eng.all_buckets_ready()        # chained form: one "gradients complete" barrier for the whole buffer
+        else:
+            for b in range(nb): eng.bucket_ready(b)
         eng.wait_allreduce()
         torch.cuda.synchronize()
         gl = [torch.empty_like(g) for _ in range(world)]

@@ -22,7 +22,9 @@ sizes = [c * 4 / 2**20 for _, c in eng.buckets]
 def step(record=None):
     ev = lambda: torch.cuda.Event(enable_timing=True)
     t0 = ev(); t0.record()
-    for b in range(nb): eng.bucket_ready(b)
+    if len(sys.argv) > 4 and sys.argv[4] == "chained": eng.all_buckets_ready()
+    else:
+        for b in range(nb): eng.bucket_ready(b)
     opt.step_count += 1
     marks = []
     for b in range(nb):
@@ -38,7 +40,7 @@ for _ in range(20): step(rec)
 torch.cuda.synchronize()
 if rank == 0:
     import statistics as st
-    print(f"W={world} mode={mode} cap={cap} overlap_blocks_per_sm={sys.argv[3] if len(sys.argv) > 3 else 0} buckets MB={[round(s,1) for s in sizes]}")
+    print(f"W={world} mode={mode} cap={cap} overlap_blocks_per_sm={sys.argv[3] if len(sys.argv) > 3 else 0} {sys.argv[4] if len(sys.argv) > 4 else "per-bucket"} buckets MB={[round(s,1) for s in sizes]}")
     for b in range(nb):
         tw = st.mean(t0.elapsed_time(m[b][0]) for t0, m, f in rec); tu = st.mean(t0.elapsed_time(m[b][1]) for t0, m, f in rec)
         print(f"  bucket {b} ({sizes[b]:6.1f} MB): all-reduce visible at {tw:.3f} ms, update done at {tu:.3f} ms (update span {tu-tw:.3f})")
