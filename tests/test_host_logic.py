@@ -122,3 +122,73 @@ def test_logger_running_mean_and_dump(tmp_path):
     assert logger.getkvs() == {}
     assert (tmp_path / "progress.csv").exists()
     assert logger.get_current().dir == str(tmp_path)
+
+
+class _StubEngine:
+    """Engine stand-in for host-only tests of FusedAdamW's bookkeeping (no kernels run)."""
+
+    def __init__(self, layout, dtype, device, ema_rates=(), betas=(0.9, 0.999), eps=1e-8, **kw):
+        self.layout, self.betas, self.eps, self.world_size, self.nvls = layout, tuple(betas), eps, 1, False
+        self.calls = []
+
+    def bind(self, *a):
+        pass
+
+    def fused_update(self, lr, wd, step, **kw):
+        self.calls.append(("update", lr, wd, step, kw))
+
+    def grad_norm(self, inv_scale, max_norm):
+        self.calls.append(("norm", inv_scale, max_norm))
+
+    def zero_grads(self):
+        self.calls.append(("zero",))
+
+
+def test_fused_adamw_state_dict_is_torch_adamw_layout(monkeypatch):
+    """opt_NNNNNN.pt must be interchangeable with torch.optim.AdamW's (reference :165-173, :296-302)."""
+    from distributed_pipeline_b200 import optim as optim_mod
+    monkeypatch.setattr(optim_mod, "Engine", _StubEngine)
+    torch.manual_seed(0)
+    params = [torch.nn.Parameter(torch.randn(5, 3)), torch.nn.Parameter(torch.randn(7)), torch.nn.Parameter(torch.randn(2, 2, 2))]
+    ours = optim_mod.FusedAdamW(params, lr=1e-3, weight_decay=0.01, ema_rates=[0.99])
+    assert ours.state_dict()["state"] == {} and ours.state == {}        # like torch before the first step
+    ours.clip_grad_norm(1.0)
+    ours.step()
+    assert [c[0] for c in ours.engine.calls] == ["norm", "update"]
+    assert ours.engine.calls[1][3] == 1 and ours.engine.calls[1][4]["use_clip_coef"] is True
+    ours.step()
+    assert ours.engine.calls[2][4]["use_clip_coef"] is False              # the coefficient is used once
+    assert ours.ema_done == [True]
+
+    stock_params = [torch.nn.Parameter(p.detach().clone()) for p in params]
+    stock = torch.optim.AdamW(stock_params, lr=1e-3, weight_decay=0.01)
+    for p in stock_params:
+        p.grad = torch.randn_like(p)
+    stock.step()
+    stock.step()
+    a, b = ours.state_dict(), stock.state_dict()
+    assert set(a) == set(b) == {"state", "param_groups"}
+    assert list(a["state"]) == list(b["state"]) == [0, 1, 2]
+    for i in range(3):
+        assert set(a["state"][i]) == set(b["state"][i]) == {"step", "exp_avg", "exp_avg_sq"}
+        assert float(a["state"][i]["step"]) == float(b["state"][i]["step"]) == 2.0
+        assert a["state"][i]["exp_avg"].shape == b["state"][i]["exp_avg"].shape
+    assert a["param_groups"][0]["params"] == b["param_groups"][0]["params"] == [0, 1, 2]
+    assert set(b["param_groups"][0]) <= set(a["param_groups"][0])
+    # a stock checkpoint loads into the fused optimizer (moments land in the flat buffers) ...
+    ours.load_state_dict(b)
+    assert ours.step_count == 2
+    for i, p in enumerate(stock_params):
+        assert torch.equal(ours.flat.exp_avg_views[i], stock.state[p]["exp_avg"])
+        assert torch.equal(ours.flat.exp_avg_sq_views[i], stock.state[p]["exp_avg_sq"])
+    # ... and ours loads into a stock AdamW
+    fresh = torch.optim.AdamW([torch.nn.Parameter(p.detach().clone()) for p in params], lr=1e-3, weight_decay=0.01)
+    fresh.load_state_dict(ours.state_dict())
+    assert float(next(iter(fresh.state.values()))["step"]) == 2.0
+    # mismatching layouts are refused
+    with pytest.raises(ValueError):
+        ours.load_state_dict({"state": {}, "param_groups": [{"params": [0]}]})
+    with pytest.raises(ValueError):
+        ours.zero_grad(set_to_none=True)
+    with pytest.raises(NotImplementedError):
+        ours.step(closure=lambda: None)
