@@ -25,6 +25,7 @@ E_BADARG, E_NCCL, E_STATE, E_NOMEM, E_LIMIT = -1, -2, -3, -4, -5
 STATIC_MAX_ELEMS = 536870912
 OPT_OVERLAP_BLOCKS_PER_SM = 1
 OPT_NORM_STAGING = 2
+OPT_PEER_TIMEOUT_MS = 3
 
 
 class DpkError(RuntimeError):
@@ -83,6 +84,7 @@ SIGNATURES = {
                                            C.c_int32, C.c_int32, _VP]),
     "dpk_fused_update_finish": (C.c_int, [_VP, C.c_int32, _VP]),
     "dpk_reduce_update_pair": (C.c_int, [_VP, C.c_double, C.c_double, C.c_int64, C.c_double, _VP]),
+    "dpk_reduce_update": (C.c_int, [_VP, C.c_double, C.c_double, C.c_int64, C.c_double, _VP]),
     "dpk_set_option": (C.c_int, [_VP, C.c_int32, C.c_int64]),
     "dpk_result_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),
     "dpk_read_result_sync": (C.c_int, [_VP, C.POINTER(C.c_double), _VP]),

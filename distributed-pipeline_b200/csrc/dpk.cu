@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <new>
@@ -105,37 +106,10 @@ static int grid_for(Kern kern, int n_work, int sm_count, int* out) {
   return 0;
 }
 
-// Optional CUDA-event bracket around one streaming kernel (bench instrumentation).
-struct KernelTimer {
-  dpk_handle* h;
-  int which;
-  cudaStream_t st;
-  cudaEvent_t end = nullptr;
-  KernelTimer(dpk_handle* h_, int which_, cudaStream_t st_) : h(h_), which(which_), st(st_) {
-    if (!h->timing || h->tcount[which] >= DPK_TIMING_SLOTS) return;
-    auto& v = h->tev[which];
-    const size_t need = 2 * (size_t)(h->tcount[which] + 1);
-    while (v.size() < need) {
-      cudaEvent_t e = nullptr;
-      if (cudaEventCreate(&e) != cudaSuccess) return;
-      v.push_back(e);
-    }
-    cudaEventRecord(v[need - 2], st);
-    end = v[need - 1];
-  }
-  ~KernelTimer() {
-    if (end) {
-      cudaEventRecord(end, st);
-      h->tcount[which]++;
-    }
-  }
-};
-
 // ---- pass 1 ---------------------------------------------------------------
 
 template <typename T>
-static int launch_sumsq(dpk_handle* h, int tile_begin, int tile_end, float inv_scale,
-                        cudaStream_t st) {
+static int launch_sumsq(dpk_handle* h, int tile_begin, int tile_end, float inv_scale, cudaStream_t st) {
   const int n = tile_end - tile_begin;
   if (n <= 0) return 0;
   if (h->norm_staging) {
@@ -169,16 +143,6 @@ static int launch_sumsq(dpk_handle* h, int tile_begin, int tile_end, float inv_s
   return 0;
 }
 
-static int launch_segment_reduce(dpk_handle* h, const TilePartial* partials, int per_tile, cudaStream_t st) {
-  if (h->n_seg == 0) return 0;
-  const int grid = std::min(h->n_seg, 4 * h->sm_count);
-  segment_reduce_kernel<<<grid, kThreads, 0, st>>>(partials, h->d_seg_tile_begin, h->d_seg_sumsq,
-                                                   h->d_seg_bad, h->n_seg, per_tile);
-  h->launches++;
-  DPK_CUDA(cudaGetLastError());
-  return 0;
-}
-
 // ---- pass 2 ---------------------------------------------------------------
 
 template <typename T, int K, int GM>
@@ -191,6 +155,7 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
   for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
   a.peer_g = (GM == kGradPair) ? (const T*)h->peer_grads[1 - h->rank] : nullptr;
+  a.unit_flags = nullptr; a.flag_target = 0; a.unit_shift = 0; a.timeout_ns = 0; a.results_rw = h->d_results;
   a.tiles = h->d_tiles;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
@@ -201,7 +166,12 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   a.use_clip_coef = use_coef;
   a.skip_if_nonfinite = skip;
   a.s = sc;
-  auto kern = fused_update_kernel<T, K, GM>;
+  void (*kern)(const UpdateArgs<T, K>) = fused_update_kernel<T, K, GM>;
+  if constexpr (sizeof(T) == 2 && K <= 2) {
+    // bf16: 4 resident blocks/SM cap the kernel at 64 registers (a few spills), 3 give
+    // it 80; which wins is a measurement (tuning knob, same results)
+    if (h->update_blocks_per_sm == 3) kern = fused_update_kernel<T, K, GM, 3>;
+  }
   int grid = 0;
   const long long items = (long long)n_tiles * h->chunks_per_tile;
   if (int rc = grid_for(kern, (int)std::min<long long>(items, 1 << 30), h->sm_count, &grid)) return rc;
@@ -261,17 +231,19 @@ static void release_device_state(dpk_handle* h) {
   cudaFree(h->d_seg_sumsq);
   cudaFree(h->d_seg_bad);
   cudaFree(h->d_seg_norms);
+  cudaFree(h->d_counters);
   cudaFree(h->d_results);
   h->d_tiles = nullptr; h->d_seg_tile_begin = nullptr;
   h->d_partials_pre = h->d_partials_post = nullptr;
-  h->d_seg_sumsq = nullptr; h->d_seg_bad = nullptr; h->d_seg_norms = nullptr; h->d_results = nullptr;
+  h->d_seg_sumsq = nullptr; h->d_seg_bad = nullptr; h->d_seg_norms = nullptr; h->d_counters = nullptr;
+  h->d_results = nullptr;
   if (h->h_results_pinned) cudaFreeHost(h->h_results_pinned);
   h->h_results_pinned = nullptr;
   for (auto& v : h->tev) {
     for (cudaEvent_t e : v) cudaEventDestroy(e);
     v.clear();
   }
-  h->tcount[0] = h->tcount[1] = 0;
+  h->tcount[0] = h->tcount[1] = h->tcount[2] = 0;
 }
 
 static void free_handle(dpk_handle* h) {
@@ -308,6 +280,8 @@ static int create_device_state(dpk_handle* h) {
   DPK_CUDA(cudaMalloc(&h->d_seg_sumsq, ns * sizeof(double)));
   DPK_CUDA(cudaMalloc(&h->d_seg_bad, ns * sizeof(unsigned)));
   DPK_CUDA(cudaMalloc(&h->d_seg_norms, ns * sizeof(double)));
+  DPK_CUDA(cudaMalloc(&h->d_counters, 2 * sizeof(unsigned)));
+  DPK_CUDA(cudaMemset(h->d_counters, 0, 2 * sizeof(unsigned)));
   DPK_CUDA(cudaMallocHost(&h->h_results_pinned, DPK_R_COUNT * sizeof(double)));
   if (!h->tiles.empty())
     DPK_CUDA(cudaMemcpy(h->d_tiles, h->tiles.data(), h->tiles.size() * sizeof(Tile), cudaMemcpyHostToDevice));
@@ -388,6 +362,12 @@ int dpk_create(dpk_handle** out, const dpk_config* cfg) {
   h->chunks_per_tile = tile_elems / h->chunk_elems;
   h->n_elems = cfg->n_elems;
   h->beta1 = cfg->beta1; h->beta2 = cfg->beta2; h->eps = cfg->eps;
+  if (const char* e = getenv("DPK_FORCE_MULTIMEM")) h->force_multimem = atoi(e) != 0;
+  if (const char* e = getenv("DPK_UPDATE_BLOCKS_PER_SM")) h->update_blocks_per_sm = atoi(e);
+  if (const char* e = getenv("DPK_PEER_TIMEOUT_MS")) {
+    const long long ms = atoll(e);
+    if (ms > 0) h->peer_timeout_ns = (unsigned long long)ms * 1000000ull;
+  }
   for (int k = 0; k < cfg->n_ema; ++k) h->ema_rates[k] = cfg->ema_rates[k];
 
   // segments: ascending, 16-byte aligned starts, ragged tails stay inside the gap
@@ -570,6 +550,7 @@ static int enqueue_bucket(dpk_handle* h, int b, cudaStream_t producer, bool chai
     DPK_CUDA(cudaEventRecord(h->ev_ready, producer));
     DPK_CUDA(cudaStreamWaitEvent(h->comm_stream, h->ev_ready, 0));
   }
+  KernelTimer timer(h, 2, h->comm_stream);  // instrumentation: this bucket's collective alone
   if (h->mc_grads) {
     // our own all-reduce over symmetric memory (dpk_nvls.cu)
     if (int rc = nvls_allreduce(h, bk, !chained, h->comm_stream)) return rc;
@@ -580,6 +561,7 @@ static int enqueue_bucket(dpk_handle* h, int b, cudaStream_t producer, bool chai
     DPK_NCCL(api->AllReduce(base, base, (size_t)bk.count, h->dtype == DPK_F32 ? ncclFloat32 : ncclBfloat16,
                             ncclAvg, h->comm, h->comm_stream));
   }
+  timer.stop();
   DPK_CUDA(cudaEventRecord(h->ev_bucket_done[b], h->comm_stream));
   DPK_CUDA(cudaEventRecord(h->ev_done, h->comm_stream));
   h->bucket_pending[b] = 1;
@@ -695,13 +677,16 @@ int dpk_grad_norm_finish(dpk_handle* h, double max_norm, void* stream) {
   if (!h->bound) { set_error("dpk_grad_norm: buffers not bound"); return DPK_E_STATE; }
   DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
-  if (int rc = launch_segment_reduce(h, h->d_partials_pre, 1, st)) return rc;
+  const int grid = std::max(1, std::min(h->n_seg, 4 * h->sm_count));
+  unsigned* ticket = h->d_counters;
   if (h->dtype == DPK_F32)
-    finalize_norm_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->d_seg_bad, h->n_seg, (float)max_norm,
-                                                        h->d_seg_norms, h->d_results);
+    norm_tail_kernel<float><<<grid, kThreads, 0, st>>>(h->d_partials_pre, h->d_seg_tile_begin, h->d_seg_sumsq,
+                                                       h->d_seg_bad, h->n_seg, (float)max_norm, h->d_seg_norms,
+                                                       h->d_results, ticket);
   else
-    finalize_norm_kernel<__nv_bfloat16><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->d_seg_bad, h->n_seg,
-                                                                (float)max_norm, h->d_seg_norms, h->d_results);
+    norm_tail_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>(h->d_partials_pre, h->d_seg_tile_begin, h->d_seg_sumsq,
+                                                               h->d_seg_bad, h->n_seg, (float)max_norm,
+                                                               h->d_seg_norms, h->d_results, ticket);
   h->launches++;
   DPK_CUDA(cudaGetLastError());
   return 0;
@@ -712,9 +697,40 @@ int dpk_grad_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream
   return dpk_grad_norm_finish(h, max_norm, stream);
 }
 
+// Python-double arithmetic of torch's _multi_tensor_adam (optim/adam.py:770-781),
+// each value then narrowed to fp32 as a kernel argument.
+static StepScalars step_scalars(const dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
+                                double inv_scale) {
+  StepScalars sc;
+  memset(&sc, 0, sizeof(sc));
+  const double step = (double)adam_step;
+  const double bc1 = 1.0 - pow(h->beta1, step);
+  const double bc2 = 1.0 - pow(h->beta2, step);
+  sc.inv_scale = (float)inv_scale;
+  sc.decay = (float)(1.0 - lr * weight_decay);
+  sc.has_decay = weight_decay != 0.0;
+  sc.w1 = (float)(1.0 - h->beta1);
+  sc.beta2 = (float)h->beta2;
+  sc.omb2 = (float)(1.0 - h->beta2);
+  sc.bc2_sqrt = (float)pow(bc2, 0.5);
+  sc.bc2_rcp = (float)(1.0 / (double)sc.bc2_sqrt);  // correctly rounded reciprocal of the fp32 divisor
+  sc.eps = (float)h->eps;
+  sc.neg_step = (float)((lr / bc1) * -1.0);
+  for (int k = 0; k < h->n_ema; ++k) {
+    sc.rate[k] = (float)h->ema_rates[k];
+    sc.alpha[k] = (float)(1.0 - h->ema_rates[k]);
+  }
+  return sc;
+}
+
 static int update_range(dpk_handle* h, int tb, int te, double lr, double weight_decay, int64_t adam_step,
                         double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
-                        cudaStream_t st);
+                        cudaStream_t st) {
+  const StepScalars sc = step_scalars(h, lr, weight_decay, adam_step, inv_scale);
+  return (h->dtype == DPK_F32)
+             ? launch_update<float>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, tb, te, st)
+             : launch_update<__nv_bfloat16>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, tb, te, st);
+}
 
 int dpk_fused_update_bucket(dpk_handle* h, int32_t bucket, double lr, double weight_decay, int64_t adam_step,
                             double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
@@ -754,34 +770,27 @@ int dpk_reduce_update_pair(dpk_handle* h, double lr, double weight_decay, int64_
   return dpk_fused_update_finish(h, 0, stream);
 }
 
-static int update_range(dpk_handle* h, int tb, int te, double lr, double weight_decay, int64_t adam_step,
-                        double inv_scale, int32_t use_clip_coef, int32_t skip_if_nonfinite, int32_t grad_mode,
-                        cudaStream_t st) {
-
-  // Python-double arithmetic of torch's _multi_tensor_adam (optim/adam.py:770-781),
-  // each value then narrowed to fp32 as a kernel argument.
-  StepScalars sc;
-  memset(&sc, 0, sizeof(sc));
-  const double step = (double)adam_step;
-  const double bc1 = 1.0 - pow(h->beta1, step);
-  const double bc2 = 1.0 - pow(h->beta2, step);
-  sc.inv_scale = (float)inv_scale;
-  sc.decay = (float)(1.0 - lr * weight_decay);
-  sc.has_decay = weight_decay != 0.0;
-  sc.w1 = (float)(1.0 - h->beta1);
-  sc.beta2 = (float)h->beta2;
-  sc.omb2 = (float)(1.0 - h->beta2);
-  sc.bc2_sqrt = (float)pow(bc2, 0.5);
-  sc.bc2_rcp = (float)(1.0 / (double)sc.bc2_sqrt);  // correctly rounded reciprocal of the fp32 divisor
-  sc.eps = (float)h->eps;
-  sc.neg_step = (float)((lr / bc1) * -1.0);
-  for (int k = 0; k < h->n_ema; ++k) {
-    sc.rate[k] = (float)h->ema_rates[k];
-    sc.alpha[k] = (float)(1.0 - h->ema_rates[k]);
+// Any number of ranks: the gradient all-reduce (torch DDP's reducer,
+// utils/trainer.py:118-125) and optimize() (:237-244) as one kernel.  Two ranks
+// take the peer-exchange form above; four or more the switch-reduced form of
+// dpk_nvls.cu (reduce_update_kernel), whose gradient buffers end up holding the
+// averaged gradient exactly as after dpk_all_buckets_ready.
+int dpk_reduce_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step, double inv_scale,
+                      void* stream) {
+  if (!h) { set_error("dpk_reduce_update: null handle"); return DPK_E_BADARG; }
+  if (!h->bound || !h->mc_grads || h->world < 2) {
+    set_error("dpk_reduce_update: needs two or more ranks and dpk_bind_nvls");
+    return DPK_E_STATE;
   }
-  return (h->dtype == DPK_F32)
-             ? launch_update<float>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, tb, te, st)
-             : launch_update<__nv_bfloat16>(h, sc, use_clip_coef, skip_if_nonfinite, grad_mode, tb, te, st);
+  if (h->world == 2 && !h->force_multimem) return dpk_reduce_update_pair(h, lr, weight_decay, adam_step, inv_scale, stream);
+  if (adam_step < 1) { set_error("dpk_reduce_update: adam_step %lld < 1", (long long)adam_step); return DPK_E_BADARG; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = pair_sync(h, st)) return rc;  // every rank's gradients are complete
+  const StepScalars sc = step_scalars(h, lr, weight_decay, adam_step, inv_scale);
+  if (int rc = launch_reduce_update(h, sc, st)) return rc;
+  return dpk_fused_update_finish(h, 0, stream);
 }
 
 int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stream) {
@@ -789,12 +798,16 @@ int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stre
   if (!h->bound) { set_error("dpk_fused_update: buffers not bound"); return DPK_E_STATE; }
   DPK_GUARD(h);
   cudaStream_t st = (cudaStream_t)stream;
-  if (int rc = launch_segment_reduce(h, h->d_partials_post, h->chunks_per_tile, st)) return rc;
+  const int grid = std::max(1, std::min(h->n_seg, 4 * h->sm_count));
+  unsigned* ticket = h->d_counters + 1;
   if (h->dtype == DPK_F32)
-    finalize_logged_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, skip_if_nonfinite, h->d_results);
+    logged_tail_kernel<float><<<grid, kThreads, 0, st>>>(h->d_partials_post, h->d_seg_tile_begin, h->d_seg_sumsq,
+                                                         h->n_seg, h->chunks_per_tile, skip_if_nonfinite, h->d_results,
+                                                         ticket);
   else
-    finalize_logged_kernel<__nv_bfloat16><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, skip_if_nonfinite,
-                                                                 h->d_results);
+    logged_tail_kernel<__nv_bfloat16><<<grid, kThreads, 0, st>>>(h->d_partials_post, h->d_seg_tile_begin,
+                                                                 h->d_seg_sumsq, h->n_seg, h->chunks_per_tile,
+                                                                 skip_if_nonfinite, h->d_results, ticket);
   h->launches++;
   DPK_CUDA(cudaGetLastError());
   return 0;
@@ -822,6 +835,10 @@ int dpk_set_option(dpk_handle* h, int32_t option, int64_t value) {
         return DPK_E_LIMIT;
       }
       h->norm_staging = (int)value;
+      return 0;
+    case DPK_OPT_PEER_TIMEOUT_MS:
+      if (value < 1) { set_error("dpk_set_option: timeout must be at least 1 ms"); return DPK_E_BADARG; }
+      h->peer_timeout_ns = (unsigned long long)value * 1000000ull;
       return 0;
     default:
       set_error("dpk_set_option: unknown option %d", option);
@@ -858,7 +875,7 @@ int dpk_timing_enable(dpk_handle* h, int32_t on) {
 }
 
 int dpk_timing_read_sync(dpk_handle* h, int32_t which, float* ms_out, int32_t cap, int32_t* n_out) {
-  if (!h || which < 0 || which > 1 || !n_out || (cap > 0 && !ms_out)) {
+  if (!h || which < 0 || which > 2 || !n_out || (cap > 0 && !ms_out)) {
     set_error("dpk_timing_read_sync: bad argument");
     return DPK_E_BADARG;
   }

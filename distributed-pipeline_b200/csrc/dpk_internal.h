@@ -54,7 +54,8 @@ struct Bucket;
 struct dpk_handle;
 namespace dpk {
 int nvls_allreduce(dpk_handle* h, const Bucket& bk, bool start_barrier, cudaStream_t st);
-int pair_sync(dpk_handle* h, cudaStream_t st);
+int pair_sync(dpk_handle* h, cudaStream_t st);  // barrier between all ranks, a kernel of its own
+int launch_reduce_update(dpk_handle* h, const StepScalars& sc, cudaStream_t st);
 
 struct Bucket {
   int seg_begin, seg_end;     // tensors [seg_begin, seg_end)
@@ -74,6 +75,7 @@ struct dpk_handle {
   int chunks_per_tile = 1;
   int overlap_blocks_per_sm = 0;  // DPK_OPT_OVERLAP_BLOCKS_PER_SM
   int norm_staging = 0;           // DPK_OPT_NORM_STAGING
+  int update_blocks_per_sm = 0;   // $DPK_UPDATE_BLOCKS_PER_SM: 3 = the 80-register build of the bf16 fused kernel
   long long n_elems = 0;
   double beta1 = 0.9, beta2 = 0.999, eps = 1e-8;
   double ema_rates[DPK_MAX_EMA] = {0};
@@ -96,6 +98,7 @@ struct dpk_handle {
   double* d_seg_sumsq = nullptr;
   unsigned* d_seg_bad = nullptr;
   double* d_seg_norms = nullptr;
+  unsigned* d_counters = nullptr;  // "last block done" tickets of the two tail kernels (zero between launches)
   double* d_results = nullptr;
   double* h_results_pinned = nullptr;
 
@@ -116,14 +119,51 @@ struct dpk_handle {
   unsigned* mc_signal = nullptr;
   const unsigned* local_signal = nullptr;
   int nvls_blocks = 0;
+  bool force_multimem = false;  // $DPK_FORCE_MULTIMEM=1: two ranks take the switch (W >= 4) kernels too (development)
   int nvls_slots = 0;
   unsigned pair_sig = 0;  // value of the last slot's counter after the pair barriers enqueued so far
   int nvls_unroll = 4;
   unsigned nvls_sig = 0;  // value of every block counter after the launches enqueued so far
+  // fused W-rank pass: per-unit arrival counters inside the signal array
+  int flag_base = 0, flag_slots = 0;
+  unsigned flag_epoch = 0;   // value every unit counter has after the steps enqueued so far
+  int unit_shift = 0;        // log2(vectors per unit)
+  int fused_comm_blocks = 64, fused_update_blocks = 0;
+  unsigned long long peer_timeout_ns = 600ull * 1000 * 1000 * 1000;  // DPK_OPT_PEER_TIMEOUT_MS
 
   // instrumentation
   bool timing = false;
-  std::vector<cudaEvent_t> tev[2];  // [which] -> begin,end,begin,end,...
-  int tcount[2] = {0, 0};
+  std::vector<cudaEvent_t> tev[3];  // [which] -> begin,end,begin,end,...
+  int tcount[3] = {0, 0, 0};
   long long launches = 0;
 };
+
+// Optional CUDA-event bracket around one streaming kernel (bench instrumentation).
+namespace dpk {
+struct KernelTimer {
+  dpk_handle* h;
+  int which;
+  cudaStream_t st;
+  cudaEvent_t end = nullptr;
+  KernelTimer(dpk_handle* h_, int which_, cudaStream_t st_) : h(h_), which(which_), st(st_) {
+    if (!h->timing || h->tcount[which] >= DPK_TIMING_SLOTS) return;
+    auto& v = h->tev[which];
+    const size_t need = 2 * (size_t)(h->tcount[which] + 1);
+    while (v.size() < need) {
+      cudaEvent_t e = nullptr;
+      if (cudaEventCreate(&e) != cudaSuccess) return;
+      v.push_back(e);
+    }
+    cudaEventRecord(v[need - 2], st);
+    end = v[need - 1];
+  }
+  void stop() {
+    if (end) {
+      cudaEventRecord(end, st);
+      h->tcount[which]++;
+      end = nullptr;
+    }
+  }
+  ~KernelTimer() { stop(); }
+};
+}  // namespace dpk

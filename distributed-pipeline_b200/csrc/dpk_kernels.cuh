@@ -28,7 +28,7 @@ struct Tile {
   int seg;          // parameter tensor it belongs to
 };
 
-struct TilePartial {
+struct alignas(8) TilePartial {
   float sumsq;
   unsigned bad;  // 1 if a non-finite gradient element was seen
 };
@@ -88,49 +88,75 @@ template <> struct ElemTraits<float> {
   static __device__ __forceinline__ float rnd(float x) { return x; }
   // the same for a whole vector, in place
   static __device__ __forceinline__ void rndv(float*) {}
-  // a 16-byte vector is processed in chunks of four elements
   // sqrt whose result is about to be stored in the state dtype
   static __device__ __forceinline__ float sqrt_for_store(float x) { return __fsqrt_rn(x); }
+  // a 16-byte vector is processed in CH chunks of four elements
   static constexpr int CH = 1;
   static __device__ __forceinline__ void unpack4(const uint4& r, int, float* x) { unpack(r, x); }
-  static __device__ __forceinline__ void pack4(uint4& r, int, const float* x) { r = pack(x); }
   static __device__ __forceinline__ void rnd4(float*) {}
+  // round four values to the state dtype, leave them (rounded) in x and put them
+  // into chunk c of the output vector
+  static __device__ __forceinline__ void rnd4_store(float* x, uint4& r, int) { r = pack(x); }
+  // the same when the rounded values are not needed afterwards
+  static __device__ __forceinline__ void rnd4_store_only(const float* x, uint4& r, int) { r = pack(x); }
+  // acc += rnd(t[j]) for the first n of four values, in index order
+  static __device__ __forceinline__ void rnd4_accumulate(const float* t, int n, float& acc) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (j < n) acc = __fadd_rn(acc, t[j]);
+  }
+  // lanes [rem, VE) of a ragged last vector keep their old bytes
+  static __device__ __forceinline__ uint4 merge(const uint4& nw, const uint4& old, int rem) {
+    return make_uint4(rem > 0 ? nw.x : old.x, rem > 1 ? nw.y : old.y, rem > 2 ? nw.z : old.z, rem > 3 ? nw.w : old.w);
+  }
 };
 template <> struct ElemTraits<__nv_bfloat16> {
   static constexpr int VE = 8;
+  // bf16 -> fp32 of one half of a packed pair: x + (-0.0) is exact for every x,
+  // and the mixed-precision add (PTX add.f32.bf16, SASS FHADD.BF16 Rd, Rs.H0|H1, c)
+  // reads the half straight out of the packed register on the full-rate FMA
+  // pipe.  The shift / mask it replaces issue on the half-rate ALU pipe, which
+  // is what bounded the bf16 kernels (ncu round 1: ALU 46-55 %, DRAM 70 %).
+  static __device__ __forceinline__ float add_lo(unsigned w, float c) {
+    float r;
+    const unsigned short h = (unsigned short)(w & 0xffffu);
+    asm("add.f32.bf16 %0, %1, %2;" : "=f"(r) : "h"(h), "f"(c));
+    return r;
+  }
+  static __device__ __forceinline__ float add_hi(unsigned w, float c) {
+    float r;
+    const unsigned short h = (unsigned short)(w >> 16);
+    asm("add.f32.bf16 %0, %1, %2;" : "=f"(r) : "h"(h), "f"(c));
+    return r;
+  }
+  static __device__ __forceinline__ float cvt_lo(unsigned w) { return add_lo(w, -0.0f); }
+  static __device__ __forceinline__ float cvt_hi(unsigned w) { return add_hi(w, -0.0f); }
   static __device__ __forceinline__ void unpack(const uint4& r, float* x) {
-    const unsigned w[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      x[2 * i] = __uint_as_float(w[i] << 16);
-      x[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
-    }
+    x[0] = cvt_lo(r.x); x[1] = cvt_hi(r.x); x[2] = cvt_lo(r.y); x[3] = cvt_hi(r.y);
+    x[4] = cvt_lo(r.z); x[5] = cvt_hi(r.z); x[6] = cvt_lo(r.w); x[7] = cvt_hi(r.w);
   }
-  static __device__ __forceinline__ uint4 pack(const float* x) {
-    unsigned w[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      // inputs are already bf16-representable: taking the high halves is exact (one PRMT)
-      w[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
-    }
-    return make_uint4(w[0], w[1], w[2], w[3]);
-  }
-  static __device__ __forceinline__ float rnd(float x) {
-    return __bfloat162float(__float2bfloat16_rn(x));
-  }
-  // Round-to-nearest-even to bf16, two lanes per instruction.  The scalar
-  // conversion compiles to F2F.BF16.F32, which issues on the quarter-rate XU
-  // pipe and made the bf16 kernels conversion-bound (ncu: XU 77%); the packed
-  // form is F2FP.BF16.F32.PACK_AB plus two integer ops.
-  static __device__ __forceinline__ void rnd2(float& a, float& b) {
+  // Round-to-nearest-even of two fp32 values to one packed bf16 pair (a low, b
+  // high): SASS F2FP.BF16.F32.PACK_AB.  The scalar conversion would be F2F on the
+  // quarter-rate XU pipe.
+  static __device__ __forceinline__ unsigned pack2(float a, float b) {
     unsigned w;
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(b), "f"(a));
-    a = __uint_as_float(w << 16);
-    b = __uint_as_float(w & 0xffff0000u);
+    return w;
+  }
+  static __device__ __forceinline__ uint4 pack(const float* x) {  // rounds (exact on bf16-representable input)
+    return make_uint4(pack2(x[0], x[1]), pack2(x[2], x[3]), pack2(x[4], x[5]), pack2(x[6], x[7]));
+  }
+  // One value rounded to bf16 and kept as fp32: the same conversion with zero as
+  // the low half yields the fp32 bit pattern of the rounded value directly -- one
+  // instruction, nothing to unpack.
+  static __device__ __forceinline__ float rnd(float x) {
+    unsigned w;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(x), "f"(0.0f));
+    return __uint_as_float(w);
   }
   static __device__ __forceinline__ void rndv(float* x) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) rnd2(x[2 * i], x[2 * i + 1]);
+    for (int i = 0; i < 8; ++i) x[i] = rnd(x[i]);
   }
   // The square root of a bf16 value is never closer than 2^-18 (relative) to the
   // midpoint of two bf16 values (all 32 639 positive inputs enumerated), so the
@@ -139,15 +165,36 @@ template <> struct ElemTraits<__nv_bfloat16> {
   static constexpr int CH = 2;
   static __device__ __forceinline__ void unpack4(const uint4& r, int c, float* x) {
     const unsigned w0 = c ? r.z : r.x, w1 = c ? r.w : r.y;
-    x[0] = __uint_as_float(w0 << 16); x[1] = __uint_as_float(w0 & 0xffff0000u);
-    x[2] = __uint_as_float(w1 << 16); x[3] = __uint_as_float(w1 & 0xffff0000u);
+    x[0] = cvt_lo(w0); x[1] = cvt_hi(w0); x[2] = cvt_lo(w1); x[3] = cvt_hi(w1);
   }
-  static __device__ __forceinline__ void pack4(uint4& r, int c, const float* x) {
-    const unsigned w0 = __byte_perm(__float_as_uint(x[0]), __float_as_uint(x[1]), 0x7632);
-    const unsigned w1 = __byte_perm(__float_as_uint(x[2]), __float_as_uint(x[3]), 0x7632);
+  static __device__ __forceinline__ void rnd4(float* x) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = rnd(x[j]);
+  }
+  static __device__ __forceinline__ void rnd4_store(float* x, uint4& r, int c) {
+    const unsigned w0 = pack2(x[0], x[1]), w1 = pack2(x[2], x[3]);
+    x[0] = cvt_lo(w0); x[1] = cvt_hi(w0); x[2] = cvt_lo(w1); x[3] = cvt_hi(w1);
     if (c) { r.z = w0; r.w = w1; } else { r.x = w0; r.y = w1; }
   }
-  static __device__ __forceinline__ void rnd4(float* x) { rnd2(x[0], x[1]); rnd2(x[2], x[3]); }
+  static __device__ __forceinline__ void rnd4_store_only(const float* x, uint4& r, int c) {
+    const unsigned w0 = pack2(x[0], x[1]), w1 = pack2(x[2], x[3]);
+    if (c) { r.z = w0; r.w = w1; } else { r.x = w0; r.y = w1; }
+  }
+  static __device__ __forceinline__ void rnd4_accumulate(const float* t, int n, float& acc) {
+    const unsigned w0 = pack2(t[0], t[1]), w1 = pack2(t[2], t[3]);
+    if (0 < n) acc = add_lo(w0, acc);
+    if (1 < n) acc = add_hi(w0, acc);
+    if (2 < n) acc = add_lo(w1, acc);
+    if (3 < n) acc = add_hi(w1, acc);
+  }
+  static __device__ __forceinline__ unsigned merge_word(unsigned nw, unsigned old, int rem, int first) {
+    const unsigned mask = (rem > first ? 0x0000ffffu : 0u) | (rem > first + 1 ? 0xffff0000u : 0u);
+    return (nw & mask) | (old & ~mask);
+  }
+  static __device__ __forceinline__ uint4 merge(const uint4& nw, const uint4& old, int rem) {
+    return make_uint4(merge_word(nw.x, old.x, rem, 0), merge_word(nw.y, old.y, rem, 2),
+                      merge_word(nw.z, old.z, rem, 4), merge_word(nw.w, old.w, rem, 6));
+  }
 };
 
 // streaming 128-bit accesses: every byte is touched once per pass
@@ -224,6 +271,23 @@ __device__ __forceinline__ void tile_sumsq(const T* __restrict__ g_tile, int len
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (v0 + u * kThreads < nfull) {
+        if constexpr (sizeof(T) == 2) {
+          if (inv_scale == 1.0f) {
+            // bf16, no loss scale: both accumulations read the packed halves directly
+            // (FHFMA.BF16 acc, w.H0|H1, w.H0|H1, acc: the same a*a+acc in fp32, one
+            // rounding, as the FFMA on unpacked values) -- nothing to unpack
+            const unsigned w[4] = {raw[u].x, raw[u].y, raw[u].z, raw[u].w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const unsigned short lo = (unsigned short)(w[i] & 0xffffu), hi = (unsigned short)(w[i] >> 16);
+              asm("fma.rn.f32.bf16 %0, %1, %1, %0;" : "+f"(acc) : "h"(lo));
+              asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(nonfin) : "h"(lo), "h"((unsigned short)0));
+              asm("fma.rn.f32.bf16 %0, %1, %1, %0;" : "+f"(acc) : "h"(hi));
+              asm("fma.rn.f32.bf16 %0, %1, %2, %0;" : "+f"(nonfin) : "h"(hi), "h"((unsigned short)0));
+            }
+            continue;
+          }
+        }
         float x[VE];
         Tr::unpack(raw[u], x);
         if (inv_scale != 1.0f) {  // x*1 is exact: the unscale and its store only exist with a loss scale
@@ -260,8 +324,87 @@ __device__ __forceinline__ void tile_sumsq(const T* __restrict__ g_tile, int len
   }
 }
 
+// ------------------------------------------------- reduction tails (shared) --
+// Second level: one tensor's partials summed in fp64 by a whole block, thread-strided
+// then the fixed block tree: same inputs -> same bits, whoever runs it.  Partials
+// written by other blocks of the same launch are read through L2 (ld.cg).
+__device__ __forceinline__ void reduce_segment(const TilePartial* __restrict__ partials, long long b, long long e,
+                                               double* red, double& tot, int& any_bad) {
+  double acc = 0.0;
+  unsigned bad = 0;
+  for (long long t = b + threadIdx.x; t < e; t += kThreads) {
+    const uint2 raw = __ldcg(reinterpret_cast<const uint2*>(partials + t));
+    acc += (double)__uint_as_float(raw.x);
+    bad |= raw.y;
+  }
+  any_bad = __syncthreads_or((int)bad);
+  tot = block_sum_f64(acc, red);
+}
+
+// Third level (one block): per-tensor norms -> total norm -> clip coefficient,
+// rounding where torch rounds (clip_grad.py:96-108 and :165-169; for bf16 each
+// intermediate is a bf16 tensor, SURVEY F7).
+template <typename T>
+__device__ __forceinline__ void finalize_norm_block(const double* __restrict__ seg_sumsq,
+                                                    const unsigned* __restrict__ seg_bad, int n_seg, float max_norm,
+                                                    double* __restrict__ seg_norms, double* __restrict__ results,
+                                                    double* red) {
+  using Tr = ElemTraits<T>;
+  double acc = 0.0;
+  unsigned bad = 0;
+  for (int s = threadIdx.x; s < n_seg; s += kThreads) {
+    const float n = Tr::rnd(__fsqrt_rn((float)__ldcg(seg_sumsq + s)));  // _foreach_norm output
+    seg_norms[s] = (double)n;
+    acc += (double)n * (double)n;
+    bad |= __ldcg(seg_bad + s);
+  }
+  const int any_bad = __syncthreads_or((int)bad);
+  const double tot2 = block_sum_f64(acc, red);
+  if (threadIdx.x == 0) {
+    const float total = Tr::rnd(__fsqrt_rn((float)tot2));  // vector_norm(stack(norms))
+    float coef = 1.f;
+    if (max_norm > 0.f) {
+      // max_norm / (total + 1e-6) is Tensor.__rdiv__: reciprocal() * max_norm
+      const float denom = Tr::rnd(__fadd_rn(total, 1e-6f));
+      const float rcp = Tr::rnd(__fdiv_rn(1.0f, denom));
+      coef = Tr::rnd(__fmul_rn(rcp, max_norm));
+      coef = (coef > 1.0f) ? 1.0f : coef;  // clamp(max=1); NaN stays NaN
+    }
+    results[DPK_R_TOTAL_NORM] = (double)total;
+    results[DPK_R_CLIP_COEF] = (double)coef;
+    results[DPK_R_NONFINITE] = any_bad ? 1.0 : 0.0;
+  }
+}
+
+// After the fused pass: what TrainLoop._log_grad_norm computes on the grads the
+// step used -- sqrt(sum_i float64((g_i**2).sum())) (utils/trainer.py:265-271).
+// A step whose gradients were never reduced (peer timeout) or that predicated
+// itself off (non-finite under a loss scale) reports nothing new.
+template <typename T>
+__device__ __forceinline__ void finalize_logged_block(const double* __restrict__ seg_sumsq, int n_seg,
+                                                      int skip_if_nonfinite, double* __restrict__ results,
+                                                      double* red) {
+  using Tr = ElemTraits<T>;
+  const bool dead = results[DPK_R_COMM_TIMEOUT] != 0.0;
+  const bool skipped = dead || (skip_if_nonfinite && results[DPK_R_NONFINITE] != 0.0);
+  double acc = 0.0;
+  if (!skipped)
+    for (int s = threadIdx.x; s < n_seg; s += kThreads)
+      acc += (double)Tr::rnd((float)__ldcg(seg_sumsq + s));  // .sum() returns the grad dtype
+  const double tot = block_sum_f64(acc, red);
+  if (threadIdx.x == 0) {
+    if (!skipped) results[DPK_R_LOGGED_NORM] = sqrt(tot);
+    results[DPK_R_SKIPPED] = skipped ? 1.0 : 0.0;
+  }
+}
+
 // ------------------------------------------------------- pass 1: sum sq ----
 // Reads g once (s bytes/param).  One partial per tile.
+// (Finishing the reduction inside this kernel -- the block that completes a
+// tensor's last tile sums that tensor, the block that completes the last tensor
+// finalises -- was built and measured in round 2: the per-tile fence + ticket +
+// extra barrier cost 26 us on DiffuSeq-base (0.057 -> 0.083 ms), more than the
+// launch it saves.  The tail is one small launch instead: norm_tail_kernel.)
 template <typename T, int U>
 __global__ void __launch_bounds__(kThreads)
 sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin,
@@ -355,9 +498,9 @@ sumsq_tiles_tma_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, 
   }
 }
 
-// Second level: one block per tensor sums that tensor's partials in fp64.
-// `per_tile` partials were written for every tile (1 by pass 1, chunks-per-tile
-// by pass 2), laid out tile-major.
+// Stand-alone forms of the tails (the allocation-free entry point, the TMA-staged
+// variant and dpk_grad_norm_finish use them).  `per_tile` partials were written for
+// every tile (1 by pass 1, chunks-per-tile by pass 2), laid out tile-major.
 static __global__ void __launch_bounds__(kThreads)
 segment_reduce_kernel(const TilePartial* __restrict__ partials,
                       const int* __restrict__ seg_tile_begin /*[n_seg+1]*/,
@@ -365,16 +508,10 @@ segment_reduce_kernel(const TilePartial* __restrict__ partials,
                       int per_tile) {
   __shared__ double red[kThreads / 32];
   for (int s = blockIdx.x; s < n_seg; s += gridDim.x) {
-    const long long b = (long long)seg_tile_begin[s] * per_tile, e = (long long)seg_tile_begin[s + 1] * per_tile;
-    double acc = 0.0;
-    unsigned bad = 0;
-    for (long long t = b + threadIdx.x; t < e; t += kThreads) {
-      const TilePartial p = partials[t];
-      acc += (double)p.sumsq;
-      bad |= p.bad;
-    }
-    const int any_bad = __syncthreads_or((int)bad);
-    const double tot = block_sum_f64(acc, red);
+    double tot;
+    int any_bad;
+    reduce_segment(partials, (long long)seg_tile_begin[s] * per_tile, (long long)seg_tile_begin[s + 1] * per_tile,
+                   red, tot, any_bad);
     if (threadIdx.x == 0) {
       seg_sumsq[s] = tot;
       seg_bad[s] = any_bad ? 1u : 0u;
@@ -382,60 +519,69 @@ segment_reduce_kernel(const TilePartial* __restrict__ partials,
   }
 }
 
-// Third level (one block): per-tensor norms -> total norm -> clip coefficient,
-// rounding where torch rounds (clip_grad.py:96-108 and :165-169; for bf16 each
-// intermediate is a bf16 tensor, SURVEY F7).
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 finalize_norm_kernel(const double* __restrict__ seg_sumsq, const unsigned* __restrict__ seg_bad,
                      int n_seg, float max_norm, double* __restrict__ seg_norms,
                      double* __restrict__ results) {
-  using Tr = ElemTraits<T>;
   __shared__ double red[kThreads / 32];
-  double acc = 0.0;
-  unsigned bad = 0;
-  for (int s = threadIdx.x; s < n_seg; s += kThreads) {
-    const float n = Tr::rnd(__fsqrt_rn((float)seg_sumsq[s]));  // _foreach_norm output
-    seg_norms[s] = (double)n;
-    acc += (double)n * (double)n;
-    bad |= seg_bad[s];
-  }
-  const int any_bad = __syncthreads_or((int)bad);
-  const double tot2 = block_sum_f64(acc, red);
-  if (threadIdx.x == 0) {
-    const float total = Tr::rnd(__fsqrt_rn((float)tot2));  // vector_norm(stack(norms))
-    float coef = 1.f;
-    if (max_norm > 0.f) {
-      // max_norm / (total + 1e-6) is Tensor.__rdiv__: reciprocal() * max_norm
-      const float denom = Tr::rnd(__fadd_rn(total, 1e-6f));
-      const float rcp = Tr::rnd(__fdiv_rn(1.0f, denom));
-      coef = Tr::rnd(__fmul_rn(rcp, max_norm));
-      coef = (coef > 1.0f) ? 1.0f : coef;  // clamp(max=1); NaN stays NaN
-    }
-    results[DPK_R_TOTAL_NORM] = (double)total;
-    results[DPK_R_CLIP_COEF] = (double)coef;
-    results[DPK_R_NONFINITE] = any_bad ? 1.0 : 0.0;
-  }
+  finalize_norm_block<T>(seg_sumsq, seg_bad, n_seg, max_norm, seg_norms, results, red);
 }
 
-// After the fused pass: what TrainLoop._log_grad_norm computes on the grads the
-// step used -- sqrt(sum_i float64((g_i**2).sum())) (utils/trainer.py:265-271).
+// The tail of the norm pass as ONE launch: per-tensor sums (a block per tensor),
+// then -- in whichever block finishes last ("last block done": store, fence,
+// ticket) -- per-tensor norms, total norm and clip coefficient.  Every sum has a
+// fixed order, so the result does not depend on which block that is.
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-finalize_logged_kernel(const double* __restrict__ seg_sumsq, int n_seg, int skip_if_nonfinite,
-                       double* __restrict__ results) {
-  using Tr = ElemTraits<T>;
+norm_tail_kernel(const TilePartial* __restrict__ partials, const int* __restrict__ seg_tile_begin,
+                 double* __restrict__ seg_sumsq, unsigned* __restrict__ seg_bad, int n_seg, float max_norm,
+                 double* __restrict__ seg_norms, double* __restrict__ results, unsigned* __restrict__ ticket) {
   __shared__ double red[kThreads / 32];
-  const bool skipped = skip_if_nonfinite && results[DPK_R_NONFINITE] != 0.0;
-  double acc = 0.0;
-  if (!skipped)
-    for (int s = threadIdx.x; s < n_seg; s += kThreads)
-      acc += (double)Tr::rnd((float)seg_sumsq[s]);  // .sum() returns the grad dtype
-  const double tot = block_sum_f64(acc, red);
-  if (threadIdx.x == 0) {
-    if (!skipped) results[DPK_R_LOGGED_NORM] = sqrt(tot);
-    results[DPK_R_SKIPPED] = skipped ? 1.0 : 0.0;
+  for (int s = blockIdx.x; s < n_seg; s += gridDim.x) {
+    double tot;
+    int any_bad;
+    reduce_segment(partials, (long long)seg_tile_begin[s], (long long)seg_tile_begin[s + 1], red, tot, any_bad);
+    if (threadIdx.x == 0) {
+      seg_sumsq[s] = tot;
+      seg_bad[s] = any_bad ? 1u : 0u;
+    }
   }
+  int last = 0;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = (atomicAdd(ticket, 1u) + 1u == gridDim.x);
+  }
+  if (!__syncthreads_or(last)) return;
+  __threadfence();
+  finalize_norm_block<T>(seg_sumsq, seg_bad, n_seg, max_norm, seg_norms, results, red);
+  if (threadIdx.x == 0) *ticket = 0u;
+}
+
+// The tail of the fused pass as ONE launch: per-tensor sums of the per-chunk
+// partials, then -- in whichever block finishes last -- the logged norm.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+logged_tail_kernel(const TilePartial* __restrict__ partials, const int* __restrict__ seg_tile_begin,
+                   double* __restrict__ seg_sumsq, int n_seg, int per_tile, int skip_if_nonfinite,
+                   double* __restrict__ results, unsigned* __restrict__ ticket) {
+  __shared__ double red[kThreads / 32];
+  for (int s = blockIdx.x; s < n_seg; s += gridDim.x) {
+    double tot;
+    int any_bad;
+    reduce_segment(partials, (long long)seg_tile_begin[s] * per_tile, (long long)seg_tile_begin[s + 1] * per_tile,
+                   red, tot, any_bad);
+    if (threadIdx.x == 0) seg_sumsq[s] = tot;
+  }
+  int last = 0;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = (atomicAdd(ticket, 1u) + 1u == gridDim.x);
+  }
+  if (!__syncthreads_or(last)) return;
+  __threadfence();
+  finalize_logged_block<T>(seg_sumsq, n_seg, skip_if_nonfinite, results, red);
+  if (threadIdx.x == 0) *ticket = 0u;
 }
 
 // ------------------------------------------------ pass 2: the fused update --
@@ -445,6 +591,22 @@ finalize_logged_kernel(const double* __restrict__ seg_sumsq, int n_seg, int skip
 // Internal gradient mode of the two-rank fused pass: the gradient is the average
 // of this rank's and the peer's copy, taken in registers; nothing is written back.
 constexpr int kGradPair = 3;
+// Internal gradient mode of the W-rank fused pass (dpk_nvls.cu: reduce_update_kernel):
+// the averaged gradient is being written into this rank's buffer by the ranks
+// that own each range WHILE this kernel runs; a vector may be read once the
+// per-unit arrival counter says all owners have delivered their part of it.
+constexpr int kGradFlagged = 4;
+
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* addr) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ uint4 ld_sys(const uint4* p) {
   uint4 r;
@@ -462,8 +624,7 @@ __device__ __forceinline__ uint4 average2(const uint4& a, const uint4& b) {
   Tr::unpack(b, y);
 #pragma unroll
   for (int j = 0; j < Tr::VE; ++j) x[j] = __fmul_rn(__fadd_rn(x[j], y[j]), 0.5f);
-  Tr::rndv(x);
-  return Tr::pack(x);
+  return Tr::pack(x);  // rounds to the state dtype
 }
 
 template <typename T, int K>
@@ -474,6 +635,13 @@ struct UpdateArgs {
   T* v;
   T* ema[K > 0 ? K : 1];
   const T* peer_g;           // kGradPair only: the other rank's gradient buffer (peer mapping)
+  // kGradFlagged only: arrival counter of every unit of 2^unit_shift vectors, the
+  // value it has once all ranks delivered this step's average, and how long to wait
+  const unsigned* unit_flags;
+  unsigned flag_target;
+  int unit_shift;
+  unsigned long long timeout_ns;
+  double* results_rw;        // same block as `results`, writable (timeout flag)
   const Tile* tiles;
   int tile_begin, tile_end;  // this launch covers tiles [tile_begin, tile_end)
   int chunk_elems;           // elements per work item: one 16-byte vector per thread
@@ -485,8 +653,10 @@ struct UpdateArgs {
   StepScalars s;
 };
 
+// Returns true only in kGradFlagged mode, when the wait for a peer was abandoned
+// (nothing has been stored for this vector then).
 template <typename T, int K, int GM, bool FULL>
-__device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long long vidx, int rem,
+__device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long long vidx, int rem,
                                               float coef, float& acc) {
   using Tr = ElemTraits<T>;
   uint4* pv = reinterpret_cast<uint4*>(a.p) + vidx;
@@ -495,7 +665,8 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
   uint4* vv = reinterpret_cast<uint4*>(a.v) + vidx;
 
   // all loads of this vector are issued before any arithmetic
-  uint4 rg = (GM == DPK_GRAD_KEEP || GM == kGradPair) ? ld_readonly(gv) : ld_stream(gv);
+  uint4 rg = make_uint4(0, 0, 0, 0);
+  if (GM != kGradFlagged) rg = (GM == DPK_GRAD_KEEP || GM == kGradPair) ? ld_readonly(gv) : ld_stream(gv);
   uint4 rpeer = make_uint4(0, 0, 0, 0);
   if (GM == kGradPair) rpeer = ld_sys(reinterpret_cast<const uint4*>(a.peer_g) + vidx);  // over NVLink
   const uint4 rp = ld_stream(pv);
@@ -504,10 +675,27 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
   uint4 re[K > 0 ? K : 1];
 #pragma unroll
   for (int k = 0; k < K; ++k) re[k] = ld_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx);
+  if (GM == kGradFlagged) {
+    // the state loads above are in flight while this thread waits for the owners of
+    // its vector's unit; the acquire orders the gradient load behind their stores
+    const unsigned* flag = a.unit_flags + (vidx >> a.unit_shift);
+    if ((int)(ld_acquire_sys_u32(flag) - a.flag_target) < 0) {
+      const unsigned long long t0 = global_timer_ns();
+      unsigned spins = 0;
+      while ((int)(ld_acquire_sys_u32(flag) - a.flag_target) < 0) {
+        __nanosleep(64);
+        if ((++spins & 0x3ffu) == 0) {
+          const bool late = global_timer_ns() - t0 > a.timeout_ns;
+          if (late) a.results_rw[DPK_R_COMM_TIMEOUT] = 1.0;
+          if (late || *reinterpret_cast<const volatile double*>(a.results + DPK_R_COMM_TIMEOUT) != 0.0) return true;
+        }
+      }
+    }
+    rg = ld_sys(gv);  // written by other GPUs during this kernel: not through the non-coherent path
+  }
 
   if (GM == kGradPair) rg = average2<T>(rg, rpeer);  // the all-reduce, without a pass of its own
 
-  // outputs start as the inputs so that lanes past a ragged end keep their bytes
   uint4 wg = rg, wp = rp, wm = rm, wv = rv;
   uint4 we[K > 0 ? K : 1];
 #pragma unroll
@@ -522,7 +710,7 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
     Tr::unpack4(rm, c, m);
     Tr::unpack4(rv, c, v);
     // Each block below is one torch kernel: compute in fp32, then the store to the
-    // state dtype (rnd4: nothing for fp32, round-to-nearest-even for bf16).
+    // state dtype (rnd4*: nothing for fp32, round-to-nearest-even for bf16).
     // grad.mul_(1/2^lg) (upstream loss-scale) and _foreach_mul_(grads, coef): a
     // factor of exactly 1 changes no bit, so those two kernels are skipped then.
     if (s.inv_scale != 1.0f) {
@@ -535,14 +723,12 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
       for (int j = 0; j < 4; ++j) g[j] = __fmul_rn(g[j], coef);
       Tr::rnd4(g);
     }
-    // (p.grad ** 2).sum(): the square is a tensor of the grad dtype; addcmul below
-    // squares again inside its own kernel, in fp32
+    if (GM == DPK_GRAD_CLIPPED) Tr::rnd4_store_only(g, wg, c);  // g is representable: packing is exact
+    // (p.grad ** 2).sum(): the square is a tensor of the grad dtype, summed in fp32;
+    // addcmul below squares again inside its own kernel, in fp32
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { t[j] = __fmul_rn(g[j], g[j]); d[j] = t[j]; }
-    Tr::rnd4(d);
-#pragma unroll
-    for (int j = 0; j < 4; ++j)
-      if (FULL || c * 4 + j < rem) acc = __fadd_rn(acc, d[j]);
+    for (int j = 0; j < 4; ++j) t[j] = __fmul_rn(g[j], g[j]);
+    Tr::rnd4_accumulate(t, FULL ? 4 : rem - c * 4, acc);
     // _foreach_mul_(params, 1 - lr*wd), skipped when wd == 0
     if (s.has_decay) {
 #pragma unroll
@@ -552,14 +738,14 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
     // _foreach_lerp_(exp_avg, grad, 1-beta1): m + w*(g-m), w < 0.5
 #pragma unroll
     for (int j = 0; j < 4; ++j) m[j] = __fmaf_rn(s.w1, __fsub_rn(g[j], m[j]), m[j]);
-    Tr::rnd4(m);
+    Tr::rnd4_store(m, wm, c);
     // _foreach_mul_(exp_avg_sq, beta2); _foreach_addcmul_(exp_avg_sq, g, g, 1-beta2)
 #pragma unroll
     for (int j = 0; j < 4; ++j) v[j] = __fmul_rn(v[j], s.beta2);
     Tr::rnd4(v);
 #pragma unroll
     for (int j = 0; j < 4; ++j) v[j] = __fmaf_rn(s.omb2, t[j], v[j]);
-    Tr::rnd4(v);
+    Tr::rnd4_store(v, wv, c);
     // _foreach_sqrt; _foreach_div_(bc2_sqrt); _foreach_add_(eps)
 #pragma unroll
     for (int j = 0; j < 4; ++j) d[j] = Tr::sqrt_for_store(v[j]);
@@ -573,30 +759,11 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
     // _foreach_addcdiv_(params, exp_avg, denom, -step_size)
 #pragma unroll
     for (int j = 0; j < 4; ++j) p[j] = __fmaf_rn(s.neg_step, __fdiv_rn(m[j], d[j]), p[j]);
-    Tr::rnd4(p);
-
-    if (GM == DPK_GRAD_ZERO) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) g[j] = 0.f;
-    }
-    if (!FULL) {  // ragged last vector of a tensor
-      float og[4], op[4], om[4], ov[4];
-      Tr::unpack4(rg, c, og);
-      Tr::unpack4(rp, c, op);
-      Tr::unpack4(rm, c, om);
-      Tr::unpack4(rv, c, ov);
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (c * 4 + j >= rem) { g[j] = og[j]; p[j] = op[j]; m[j] = om[j]; v[j] = ov[j]; }
-    }
-    Tr::pack4(wp, c, p);
-    Tr::pack4(wm, c, m);
-    Tr::pack4(wv, c, v);
-    if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) Tr::pack4(wg, c, g);
+    Tr::rnd4_store(p, wp, c);
 
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      float e[4], oe[4];
+      float e[4];
       Tr::unpack4(re[k], c, e);
       // update_ema: trg.mul_(rate).add_(src, alpha=1-rate)  (utils/trainer.py:370),
       // src being the parameters this step just produced
@@ -605,23 +772,32 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
       Tr::rnd4(e);
 #pragma unroll
       for (int j = 0; j < 4; ++j) e[j] = __fmaf_rn(s.alpha[k], p[j], e[j]);
-      Tr::rnd4(e);
-      if (!FULL) {
-        Tr::unpack4(re[k], c, oe);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          if (c * 4 + j >= rem) e[j] = oe[j];
-      }
-      Tr::pack4(we[k], c, e);
+      Tr::rnd4_store_only(e, we[k], c);
     }
   }
+  if (GM == DPK_GRAD_ZERO) wg = make_uint4(0, 0, 0, 0);
 
-  st_stream(pv, wp);
-  st_stream(mv, wm);
-  st_stream(vv, wv);
-  if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) st_stream(gv, wg);
+  if (!FULL) {  // ragged last vector of a tensor: lanes past its end keep their bytes
+    wp = Tr::merge(wp, rp, rem);
+    wm = Tr::merge(wm, rm, rem);
+    wv = Tr::merge(wv, rv, rem);
+    if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) wg = Tr::merge(wg, rg, rem);
 #pragma unroll
-  for (int k = 0; k < K; ++k) st_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx, we[k]);
+    for (int k = 0; k < K; ++k) we[k] = Tr::merge(we[k], re[k], rem);
+  }
+
+  // Store addresses are rebuilt from the (constant-bank) base pointers and an opaque
+  // copy of the index instead of being kept alive across the arithmetic: 2 live
+  // registers instead of 2 per stream, which is what the 64-register bf16 build spilled.
+  long long sidx = vidx;
+  if (sizeof(T) == 2) asm volatile("" : "+l"(sidx));
+  st_stream(reinterpret_cast<uint4*>(a.p) + sidx, wp);
+  st_stream(reinterpret_cast<uint4*>(a.m) + sidx, wm);
+  st_stream(reinterpret_cast<uint4*>(a.v) + sidx, wv);
+  if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) st_stream(reinterpret_cast<uint4*>(a.g) + sidx, wg);
+#pragma unroll
+  for (int k = 0; k < K; ++k) st_stream(reinterpret_cast<uint4*>(a.ema[k]) + sidx, we[k]);
+  return false;
 }
 
 // Work distribution.  A work item is one *chunk*: kThreads consecutive 16-byte
@@ -635,20 +811,18 @@ __device__ __forceinline__ void update_vector(const UpdateArgs<T, K>& a, long lo
 template <typename T, int K>
 constexpr int update_min_blocks() { return sizeof(T) == 4 ? (K <= 2 ? 4 : 3) : (K <= 2 ? 4 : 3); }
 
+// The persistent chunk loop of one worker block out of n_workers.
 template <typename T, int K, int GM>
-__global__ void __launch_bounds__(kThreads, update_min_blocks<T, K>())
-fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
+__device__ __forceinline__ void update_chunks(const UpdateArgs<T, K>& a, int worker, int n_workers, float coef,
+                                              float (*red)[kThreads / 32]) {
   using Tr = ElemTraits<T>;
   constexpr int VE = Tr::VE;
-  __shared__ float red[2][kThreads / 32];
-  if (a.skip_if_nonfinite && a.results[DPK_R_NONFINITE] != 0.0) return;
-  const float coef = a.use_clip_coef ? (float)a.results[DPK_R_CLIP_COEF] : 1.0f;
-  // item = tile * chunks_per_tile + chunk, advanced by gridDim.x per iteration
+  // item = tile * chunks_per_tile + chunk, advanced by n_workers per iteration
   // without a division in the loop
   const int cpt = a.chunks_per_tile;
-  const int step_tiles = gridDim.x / cpt, step_chunks = gridDim.x % cpt;
-  int tix = a.tile_begin + blockIdx.x / cpt;
-  int chunk = blockIdx.x % cpt;
+  const int step_tiles = n_workers / cpt, step_chunks = n_workers % cpt;
+  int tix = a.tile_begin + worker / cpt;
+  int chunk = worker % cpt;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
   Tile next;
@@ -669,17 +843,22 @@ fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
     const long long vbase = (tile.start + off) / VE;
     const int nfull = len > 0 ? len / VE : 0;       // vectors with every lane valid
     float acc = 0.f;
+    bool aborted = false;
     const int v = threadIdx.x;
     if (v < nfull)
-      update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
+      aborted = update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
     else if (v == nfull && len > nfull * VE)        // ragged end of a tensor: one masked vector
-      update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc);
+      aborted = update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc);
 
     // block sum, fixed order, one barrier per item (the exchange buffer alternates)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc = __fadd_rn(acc, __shfl_down_sync(0xffffffffu, acc, o));
     if (lane == 0) red[buf][warp] = acc;
-    __syncthreads();
+    if (GM == kGradFlagged) {
+      if (__syncthreads_or((int)aborted)) return;   // a peer is gone: stop, the host raises
+    } else {
+      __syncthreads();
+    }
     if (warp == 0) {
       float r = (lane < kThreads / 32) ? red[buf][lane] : 0.f;
 #pragma unroll
@@ -693,6 +872,18 @@ fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
     }
     buf ^= 1;
   }
+}
+
+template <typename T, int K, int GM, int MB = update_min_blocks<T, K>()>
+__global__ void __launch_bounds__(kThreads, MB)
+fused_update_kernel(const __grid_constant__ UpdateArgs<T, K> a) {
+  __shared__ float red[2][kThreads / 32];
+  if (a.skip_if_nonfinite && a.results[DPK_R_NONFINITE] != 0.0) return;
+  // the library's own all-reduce gave up on a peer: these gradients were never
+  // reduced, so nothing may be updated from them (the host raises with the state intact)
+  if (a.results[DPK_R_COMM_TIMEOUT] != 0.0) return;
+  const float coef = a.use_clip_coef ? (float)a.results[DPK_R_CLIP_COEF] : 1.0f;
+  update_chunks<T, K, GM>(a, blockIdx.x, gridDim.x, coef, red);
 }
 
 // ------------------------------------------------------ stand-alone EMA ----

@@ -21,36 +21,33 @@
 // grid is small enough to be co-resident, so no block ever waits for a block
 // that cannot run.
 #include <stdlib.h>
+#include <string.h>
 
 #include "dpk_internal.h"
 
 namespace dpk {
 
 constexpr int kNvlsThreads = 512;
+constexpr int kBlockSlots = 128;          // signal slots reserved for per-block counters
+constexpr int kMinSlotsForFlags = 1024;   // smaller arrays carry no unit counters (no fused W-rank pass)
 
 __device__ __forceinline__ void mc_signal_add(unsigned* mc_addr) {
   asm volatile("multimem.red.release.sys.global.add.u32 [%0], 1;" ::"l"(mc_addr) : "memory");
 }
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* addr) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
-  return v;
-}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* addr) { return ld_acquire_sys_u32(addr); }
 
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
-
-constexpr unsigned long long kPeerTimeoutNs = 30ull * 1000 * 1000 * 1000;  // a rank that is 30 s late is gone
+// How long a block waits for a peer before giving up: h->peer_timeout_ns, ten
+// minutes unless DPK_OPT_PEER_TIMEOUT_MS / $DPK_PEER_TIMEOUT_MS says otherwise
+// (the reference's NCCL watchdog default).  A rank may legitimately be late by
+// a long time: rank 0 alone runs the eval callbacks (utils/trainer.py:189-191).
 
 // All threads of the block call this.  `target` is the value this block's
 // counter reaches once all W ranks have arrived at this barrier.  A peer that
-// never arrives (crashed rank) must not hang the GPU: after kPeerTimeoutNs the
-// wait is abandoned and the sticky DPK_R_COMM_TIMEOUT flag raised for the host.
+// never arrives (crashed rank) must not hang the GPU: after timeout_ns the
+// wait is abandoned and the sticky DPK_R_COMM_TIMEOUT flag raised for the host;
+// the update kernels then leave the state alone (dpk_kernels.cuh).
 __device__ __forceinline__ void block_barrier_all_ranks(unsigned* mc_sig, const unsigned* local_sig, unsigned target,
-                                                        double* results) {
+                                                        double* results, unsigned long long timeout_ns) {
   __threadfence_system();  // this thread's multimem stores before the signal
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -58,7 +55,7 @@ __device__ __forceinline__ void block_barrier_all_ranks(unsigned* mc_sig, const 
     const unsigned long long t0 = global_timer_ns();
     unsigned spins = 0;
     while ((int)(ld_acquire_sys(local_sig + blockIdx.x) - target) < 0) {
-      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > kPeerTimeoutNs) {
+      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > timeout_ns) {
         results[DPK_R_COMM_TIMEOUT] = 1.0;
         break;
       }
@@ -95,8 +92,7 @@ template <> struct Multimem<__nv_bfloat16> {
     ElemTraits<__nv_bfloat16>::unpack(v, x);
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(x[j], s);
-    ElemTraits<__nv_bfloat16>::rndv(x);
-    return ElemTraits<__nv_bfloat16>::pack(x);
+    return ElemTraits<__nv_bfloat16>::pack(x);  // rounds to bf16
   }
 };
 
@@ -112,11 +108,11 @@ template <typename T, int kNvlsUnroll>
 __global__ void __launch_bounds__(kNvlsThreads)
 nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int rank, int world, float inv_world,
                       unsigned* mc_sig, const unsigned* local_sig, unsigned sig_base, int start_barrier,
-                      double* results) {
+                      double* results, unsigned long long timeout_ns) {
   // every rank's local gradients for this range are complete once its block b is here
   // (skipped for the later buckets of a chain whose first bucket already established it)
   if (start_barrier) {
-    block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results);
+    block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results, timeout_ns);
     sig_base += (unsigned)world;
   }
 
@@ -136,7 +132,7 @@ nvls_allreduce_kernel(uint4* mc_grads, long long vec_begin, long long n_vec, int
   }
 
   // every rank's slice has been written into every copy once all block-b's are here
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + (unsigned)world, results, timeout_ns);
 }
 
 // Two ranks: the switch has nothing to save (a multicast store also echoes the
@@ -158,9 +154,10 @@ __device__ __forceinline__ void st_peer(uint4* p, const uint4& v) {
 template <typename T, int U>
 __global__ void __launch_bounds__(kNvlsThreads)
 pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n_vec, int rank, unsigned* mc_sig,
-                      const unsigned* local_sig, unsigned sig_base, int start_barrier, double* results) {
+                      const unsigned* local_sig, unsigned sig_base, int start_barrier, double* results,
+                      unsigned long long timeout_ns) {
   if (start_barrier) {
-    block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results);
+    block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results, timeout_ns);
     sig_base += 2u;
   }
   const long long per_rank = (n_vec + 1) / 2;
@@ -184,20 +181,21 @@ pair_allreduce_kernel(uint4* mine, uint4* peer, long long vec_begin, long long n
         st_peer(mine + i + u * stride, v);
       }
   }
-  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results);
+  block_barrier_all_ranks(mc_sig, local_sig, sig_base + 2u, results, timeout_ns);
 }
 
-// A barrier between the two ranks as a kernel of its own: stream order then keeps
+// A barrier between all ranks as a kernel of its own: stream order then keeps
 // the big kernel between two of them free of any waiting.  It owns the last
 // signal slot, which no all-reduce block ever touches.
-__global__ void pair_sync_kernel(unsigned* mc_sig, const unsigned* local_sig, int slot, unsigned target, double* results) {
+__global__ void pair_sync_kernel(unsigned* mc_sig, const unsigned* local_sig, int slot, unsigned target, double* results,
+                                 unsigned long long timeout_ns) {
   __threadfence_system();
   if (threadIdx.x == 0) {
     mc_signal_add(mc_sig + slot);
     const unsigned long long t0 = global_timer_ns();
     unsigned spins = 0;
     while ((int)(ld_acquire_sys(local_sig + slot) - target) < 0) {
-      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > kPeerTimeoutNs) {
+      if ((++spins & 0xfffu) == 0 && global_timer_ns() - t0 > timeout_ns) {
         results[DPK_R_COMM_TIMEOUT] = 1.0;
         break;
       }
@@ -205,9 +203,149 @@ __global__ void pair_sync_kernel(unsigned* mc_sig, const unsigned* local_sig, in
   }
 }
 
+// ---- W ranks: gradient all-reduce AND the update in ONE kernel -----------------
+// The grid splits into two roles that run side by side on every rank:
+//   * the first n_comm blocks are the collective.  The flat gradient buffer is cut
+//     into units of 2^unit_shift vectors; of every unit each rank owns 1/W.  Comm
+//     block b walks units b, b+n_comm, ...: it pulls the switch-reduced sum of its
+//     slice (multimem.ld_reduce), scales by 1/W and multicasts the average into all
+//     W copies (multimem.st) -- the arithmetic of nvls_allreduce_kernel, so the
+//     averaged gradient is bit-identical -- then adds 1 to the unit's arrival
+//     counter on every rank (multimem.red.release).  These blocks never wait.
+//   * the other blocks are the update: the persistent chunk loop of
+//     fused_update_kernel in kGradFlagged mode.  Each thread issues the loads of
+//     p, m, v and the EMA copies, then waits until its vector's unit has collected
+//     W arrivals on THIS rank and only then loads the (averaged) gradient.
+// So the update trails the collective by one unit instead of one bucket, there is
+// no barrier between buckets and no separately launched last-bucket update.
+// Progress: update blocks wait only for comm blocks (of all ranks); comm blocks
+// wait for nothing, and being the lowest block indices they are resident first.
+// A rank_sync kernel in front establishes "every rank's gradients are complete";
+// none is needed behind: a rank leaves the kernel only after every unit arrived,
+// i.e. after every owner has both read this rank's contribution and written the
+// average back, and nobody touches a peer's buffer again before the next
+// rank_sync.  Arrival counters are monotonic: after step s they hold s*W.
+struct ReduceArgs {
+  uint4* mc_grads;        // multicast address of the flat gradient buffer
+  long long n_vec;        // 16-byte vectors in the buffer
+  int unit_shift;
+  int n_units;
+  int rank, world;
+  float inv_world;
+  unsigned* mc_flags;     // multicast address of the per-unit arrival counters
+  int n_comm;
+};
+
+template <typename T, int K, int U>
+__global__ void __launch_bounds__(kThreads, update_min_blocks<T, K>())
+reduce_update_kernel(const __grid_constant__ UpdateArgs<T, K> a, const __grid_constant__ ReduceArgs r) {
+  __shared__ float red[2][kThreads / 32];
+  if (a.results[DPK_R_COMM_TIMEOUT] != 0.0) return;  // rank_sync gave up: leave gradients and state alone
+  if ((int)blockIdx.x >= r.n_comm) {
+    update_chunks<T, K, kGradFlagged>(a, (int)blockIdx.x - r.n_comm, (int)gridDim.x - r.n_comm, 1.0f, red);
+    return;
+  }
+  const long long unit_vecs = 1ll << r.unit_shift;
+  for (int u = blockIdx.x; u < r.n_units; u += r.n_comm) {
+    const long long ulo = (long long)u << r.unit_shift;
+    long long n = r.n_vec - ulo;
+    if (n > unit_vecs) n = unit_vecs;
+    const long long per = (n + r.world - 1) / r.world;
+    const long long lo = ulo + (long long)r.rank * per;
+    long long hi = lo + per;
+    if (hi > ulo + n) hi = ulo + n;
+    for (long long i = lo + threadIdx.x; i < hi; i += (long long)kThreads * U) {
+      uint4 v[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k)
+        if (i + k * kThreads < hi) v[k] = Multimem<T>::ld_reduce(r.mc_grads + i + k * kThreads);
+#pragma unroll
+      for (int k = 0; k < U; ++k)
+        if (i + k * kThreads < hi) multimem_st(r.mc_grads + i + k * kThreads, Multimem<T>::scale(v[k], r.inv_world));
+    }
+    // every thread's stores precede the barrier, the barrier precedes thread 0's
+    // release: the arrival is ordered behind the whole slice (cumulativity)
+    __syncthreads();
+    if (threadIdx.x == 0) mc_signal_add(r.mc_flags + u);
+  }
+}
+
+template <typename T, int K>
+static int launch_reduce_update_k(dpk_handle* h, const StepScalars& sc, cudaStream_t st) {
+  UpdateArgs<T, K> a;
+  memset(&a, 0, sizeof(a));
+  a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
+  for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
+  a.tiles = h->d_tiles;
+  a.tile_begin = 0;
+  a.tile_end = (int)h->tiles.size();
+  a.chunk_elems = h->chunk_elems;
+  a.chunks_per_tile = h->chunks_per_tile;
+  a.partials = h->d_partials_post;
+  a.results = h->d_results;
+  a.results_rw = h->d_results;
+  a.s = sc;
+  a.unit_flags = h->local_signal + h->flag_base;
+  a.unit_shift = h->unit_shift;
+  a.timeout_ns = h->peer_timeout_ns;
+  h->flag_epoch += (unsigned)h->world;
+  a.flag_target = h->flag_epoch;
+  ReduceArgs r;
+  r.mc_grads = (uint4*)h->mc_grads;
+  const int ve = h->dtype == DPK_F32 ? 4 : 8;
+  r.n_vec = h->n_elems / ve;
+  r.unit_shift = h->unit_shift;
+  r.n_units = (int)((r.n_vec + (1ll << h->unit_shift) - 1) >> h->unit_shift);
+  r.rank = h->rank;
+  r.world = h->world;
+  r.inv_world = 1.0f / (float)h->world;
+  r.mc_flags = h->mc_signal + h->flag_base;
+  r.n_comm = h->fused_comm_blocks;
+  auto kern = reduce_update_kernel<T, K, 8>;
+  int occ = 0;
+  DPK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, 0));
+  if (occ < 1) occ = 1;
+  // every block must be resident at once (update blocks wait for comm blocks)
+  int grid = occ * h->sm_count;
+  if (h->fused_update_blocks > 0 && r.n_comm + h->fused_update_blocks < grid) grid = r.n_comm + h->fused_update_blocks;
+  if (grid < r.n_comm + 1) {
+    set_error("dpk_reduce_update: %d resident blocks cannot hold %d collective blocks", grid, r.n_comm);
+    return DPK_E_LIMIT;
+  }
+  {
+    KernelTimer timer(h, 0, st);
+    kern<<<grid, kThreads, 0, st>>>(a, r);
+  }
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <typename T>
+static int launch_reduce_update_t(dpk_handle* h, const StepScalars& sc, cudaStream_t st) {
+  switch (h->n_ema) {
+    case 0: return launch_reduce_update_k<T, 0>(h, sc, st);
+    case 1: return launch_reduce_update_k<T, 1>(h, sc, st);
+    case 2: return launch_reduce_update_k<T, 2>(h, sc, st);
+    case 3: return launch_reduce_update_k<T, 3>(h, sc, st);
+    default: return launch_reduce_update_k<T, 4>(h, sc, st);
+  }
+}
+
+int launch_reduce_update(dpk_handle* h, const StepScalars& sc, cudaStream_t st) {
+  if (h->flag_slots <= 0) {
+    set_error("dpk_reduce_update: the signal array bound with dpk_bind_nvls has no room for unit counters "
+              "(needs at least %d slots)", kMinSlotsForFlags);
+    return DPK_E_STATE;
+  }
+  return h->dtype == DPK_F32 ? launch_reduce_update_t<float>(h, sc, st)
+                             : launch_reduce_update_t<__nv_bfloat16>(h, sc, st);
+}
+
 int pair_sync(dpk_handle* h, cudaStream_t st) {
-  h->pair_sig += 2u;
-  pair_sync_kernel<<<1, 32, 0, st>>>(h->mc_signal, h->local_signal, h->nvls_slots - 1, h->pair_sig, h->d_results);
+  h->pair_sig += (unsigned)h->world;  // one arrival per rank
+  pair_sync_kernel<<<1, 32, 0, st>>>(h->mc_signal, h->local_signal, h->nvls_slots - 1, h->pair_sig, h->d_results,
+                                     h->peer_timeout_ns);
   DPK_CUDA(cudaGetLastError());
   h->launches++;
   return 0;
@@ -220,16 +358,17 @@ int nvls_allreduce(dpk_handle* h, const Bucket& bk, bool start_barrier, cudaStre
   // the grid never changes after dpk_bind_nvls: every block owns one counter and
   // all counters must advance in lockstep with h->nvls_sig
   const int grid = h->nvls_blocks, unroll = h->nvls_unroll;
-  if (h->world == 2) {
+  if (h->world == 2 && !h->force_multimem) {
     uint4* peer = (uint4*)h->peer_grads[1 - h->rank];
     if (h->dtype == DPK_F32)
       pair_allreduce_kernel<float, 4><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->g, peer, vec_begin, n_vec, h->rank,
                                                                     h->mc_signal, h->local_signal, h->nvls_sig, (int)start_barrier,
-                                                                    h->d_results);
+                                                                    h->d_results, h->peer_timeout_ns);
     else
       pair_allreduce_kernel<__nv_bfloat16, 4><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->g, peer, vec_begin, n_vec,
                                                                             h->rank, h->mc_signal, h->local_signal,
-                                                                            h->nvls_sig, (int)start_barrier, h->d_results);
+                                                                            h->nvls_sig, (int)start_barrier, h->d_results,
+                                                                            h->peer_timeout_ns);
     DPK_CUDA(cudaGetLastError());
     h->nvls_sig += start_barrier ? 4u : 2u;
     h->launches++;
@@ -237,7 +376,8 @@ int nvls_allreduce(dpk_handle* h, const Bucket& bk, bool start_barrier, cudaStre
   }
 #define DPK_NVLS_LAUNCH(T, U)                                                                                        \
   nvls_allreduce_kernel<T, U><<<grid, kNvlsThreads, 0, st>>>((uint4*)h->mc_grads, vec_begin, n_vec, h->rank, h->world, \
-                                                            inv_world, h->mc_signal, h->local_signal, h->nvls_sig, (int)start_barrier, h->d_results)
+                                                            inv_world, h->mc_signal, h->local_signal, h->nvls_sig, (int)start_barrier, h->d_results, \
+                                                            h->peer_timeout_ns)
   if (h->dtype == DPK_F32) {
     if (unroll == 8) DPK_NVLS_LAUNCH(float, 8); else if (unroll == 2) DPK_NVLS_LAUNCH(float, 2); else DPK_NVLS_LAUNCH(float, 4);
   } else {
@@ -286,10 +426,35 @@ extern "C" int dpk_bind_nvls(dpk_handle* h, void* mc_grads, void* const* peer_gr
   if (n_slots < 2) { set_error("dpk_bind_nvls: at least 2 signal slots"); return DPK_E_BADARG; }
   h->nvls_slots = n_slots;
   h->pair_sig = 0;
-  h->nvls_blocks = std::min<int>(n_slots - 1, 32);  // link-bound: 32 blocks x 512 threads x 4 vectors saturate NVLink (measured)
+  // Layout of the signal array: [0, block counters) one per all-reduce block;
+  // [kBlockSlots, n_slots-1) per-unit arrival counters of the fused W-rank pass
+  // (only when the array is large enough); the last slot belongs to rank_sync.
+  const int block_slots = n_slots >= kMinSlotsForFlags ? kBlockSlots : n_slots - 1;
+  h->nvls_blocks = std::min<int>(block_slots, 32);  // link-bound: 32 blocks x 512 threads x 4 vectors saturate NVLink (measured)
   h->nvls_unroll = 4;
-  if (const char* e = getenv("DPK_NVLS_BLOCKS")) h->nvls_blocks = std::max(1, std::min<int>(n_slots - 1, atoi(e)));  // tuning
+  if (const char* e = getenv("DPK_NVLS_BLOCKS")) h->nvls_blocks = std::max(1, std::min<int>(block_slots, atoi(e)));  // tuning
   if (const char* e = getenv("DPK_NVLS_UNROLL")) h->nvls_unroll = atoi(e);
   h->nvls_sig = 0;
+  h->flag_base = 0;
+  h->flag_slots = 0;
+  h->flag_epoch = 0;
+  if (n_slots >= kMinSlotsForFlags) {
+    h->flag_base = kBlockSlots;
+    h->flag_slots = n_slots - 1 - kBlockSlots;
+    // units of 2^unit_shift vectors: every rank's slice is a whole number of comm
+    // block iterations (kThreads x 8 vectors); grow the unit until the counters suffice
+    const int ve = h->dtype == DPK_F32 ? 4 : 8;
+    const long long n_vec = h->n_elems / ve;
+    int shift = 0;
+    long long want = (long long)h->world * kThreads * 8;
+    if (const char* e = getenv("DPK_FUSED_UNIT_KB")) want = std::max<long long>(1, atoll(e)) * 1024 / 16;
+    while ((1ll << shift) < want) ++shift;
+    while (((n_vec + (1ll << shift) - 1) >> shift) > h->flag_slots) ++shift;
+    h->unit_shift = shift;
+    h->fused_comm_blocks = 64;
+    if (const char* e = getenv("DPK_FUSED_COMM_BLOCKS")) h->fused_comm_blocks = std::max(1, atoi(e));
+    h->fused_update_blocks = 0;
+    if (const char* e = getenv("DPK_FUSED_UPDATE_BLOCKS")) h->fused_update_blocks = std::max(1, atoi(e));
+  }
   return 0;
 }

@@ -1,5 +1,7 @@
-// Exhaustive on-device checks of the two arithmetic shortcuts the fused kernel
-// takes (dpk_kernels.cuh: div_by_scalar, ElemTraits<bf16>::sqrt_for_store).
+// Exhaustive on-device checks of the arithmetic shortcuts the fused kernel
+// takes (dpk_kernels.cuh: div_by_scalar, ElemTraits<bf16>::sqrt_for_store, and the
+// bf16 conversions: rnd() = one packed conversion with a zero partner, cvt_lo/hi =
+// mixed-precision add of -0.0).
 #include "dpk_internal.h"
 
 namespace dpk {
@@ -12,13 +14,18 @@ namespace dpk {
 // shortcut is NOT exact; the kernel never produces such x: a square root of an
 // fp32 number is 0 or at least 2^-75.)
 __global__ void selftest_div_kernel(float c, float rc, unsigned long long* out) {
-  unsigned long long bad = 0;
+  unsigned long long bad = 0, bad_cvt = 0;
   const unsigned long long n = 1ull << 32;
   for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (unsigned long long)gridDim.x * blockDim.x) {
     const float v = __uint_as_float((unsigned)i);
     float xs[4] = {__fsqrt_rn(v), sqrt_approx(__uint_as_float((unsigned)i & 0xffff0000u)), 0.f, 0.f};
-    ElemTraits<__nv_bfloat16>::rnd2(xs[1], xs[2]);
+    xs[1] = ElemTraits<__nv_bfloat16>::rnd(xs[1]);
+    {  // rnd(v) must be the IEEE round-to-nearest-even conversion, as an fp32 value
+      const float want = __bfloat162float(__float2bfloat16_rn(v));
+      const float got = ElemTraits<__nv_bfloat16>::rnd(v);
+      if (!((want != want) && (got != got)) && __float_as_uint(want) != __float_as_uint(got)) ++bad_cvt;
+    }
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
       const float want = __fdiv_rn(xs[k], c);
@@ -31,6 +38,7 @@ __global__ void selftest_div_kernel(float c, float rc, unsigned long long* out) 
     }
   }
   if (bad) atomicAdd(out, bad);
+  if (bad_cvt) atomicAdd(out + 1, bad_cvt);
 }
 
 // every bf16 bit pattern v: bf16(sqrt.approx(v)) must equal bf16(sqrt.rn(v))
@@ -42,6 +50,12 @@ __global__ void selftest_sqrt_kernel(unsigned long long* out) {
   ElemTraits<__nv_bfloat16>::rnd4(a);
   const bool both_nan = (a[0] != a[0]) && (a[1] != a[1]);
   if (!both_nan && __float_as_uint(a[0]) != __float_as_uint(a[1])) atomicAdd(out + 1, 1ull);
+  // unpacking either half of a packed pair is exact (NaN stays NaN), whatever the other half holds
+  const unsigned other = (i * 2654435761u) >> 16;
+  const float lo = ElemTraits<__nv_bfloat16>::cvt_lo((other << 16) | i), hi = ElemTraits<__nv_bfloat16>::cvt_hi((i << 16) | other);
+  const bool is_nan = (v != v);
+  if (is_nan ? !((lo != lo) && (hi != hi)) : (__float_as_uint(lo) != (i << 16) || __float_as_uint(hi) != (i << 16)))
+    atomicAdd(out + 1, 1ull);
 }
 
 }  // namespace dpk

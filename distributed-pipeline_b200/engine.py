@@ -113,7 +113,7 @@ class Engine:
         _lib.check(self.lib.dpk_comm_init(self._h, idbuf, world, rank))
         self.world_size = world
 
-    def enable_nvls(self, grads: torch.Tensor, group=None, n_slots: int = 256):
+    def enable_nvls(self, grads: torch.Tensor, group=None, n_slots: int = 65536):
         """Route the bucket all-reduce through the library's NVLS kernel.  `grads`
         is the bound gradient buffer and must come from symmetric memory
         (FlatState(symmetric_grads=True)).  Collective: every rank calls it."""
@@ -197,6 +197,11 @@ class Engine:
         """Two ranks: all-reduce and update as one kernel (see dpk_reduce_update_pair)."""
         _lib.check(self.lib.dpk_reduce_update_pair(self._h, lr, weight_decay, adam_step, inv_scale,
                                                    _stream_ptr(stream, self.device)))
+
+    def reduce_update(self, lr: float, weight_decay: float, adam_step: int, inv_scale: float = 1.0, stream=None):
+        """Any world size >= 2: all-reduce and update as one kernel (see dpk_reduce_update)."""
+        _lib.check(self.lib.dpk_reduce_update(self._h, lr, weight_decay, adam_step, inv_scale,
+                                              _stream_ptr(stream, self.device)))
 
     @property
     def results(self) -> torch.Tensor:

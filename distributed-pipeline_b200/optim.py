@@ -37,6 +37,7 @@ class FusedAdamW:
         self.step_count = 0          # AdamW's per-parameter `step`, identical for all
         self.inv_scale = 1.0         # 1/2^lg_loss_scale for the next step
         self.skip_if_nonfinite = False
+        self.fused_reduce = True     # reduce_and_step may use the one-kernel all-reduce + update
         self._clip_pending = False
         # one flag per EMA rate: set by step(), consumed by trainer.update_ema
         self.ema_done = [False] * len(self.ema_rates)
@@ -77,11 +78,13 @@ class FusedAdamW:
         eng = self.engine
         g = self.param_groups[0]
         n = len(eng.buckets)
-        if (eng.world_size == 2 and eng.nvls and max_norm <= 0 and self.grad_mode == _lib.GRAD_KEEP
-                and not self.skip_if_nonfinite):
-            # two ranks, gradients not needed afterwards: exchange and update in ONE kernel
+        if (eng.world_size >= 2 and eng.nvls and self.fused_reduce and max_norm <= 0
+                and self.grad_mode == _lib.GRAD_KEEP and not self.skip_if_nonfinite):
+            # no clipping, gradients not rewritten: exchange and update in ONE kernel -- two ranks
+            # average each vector with the peer's in registers, four or more reduce through
+            # the switch in part of the grid while the rest updates range by range
             self.step_count += 1
-            eng.reduce_update_pair(float(g["lr"]), float(g["weight_decay"]), self.step_count, self.inv_scale)
+            eng.reduce_update(float(g["lr"]), float(g["weight_decay"]), self.step_count, self.inv_scale)
             self._clip_pending = False
             self.ema_done = [True] * len(self.ema_rates)
             return

@@ -65,7 +65,8 @@ extern "C" {
 #define DPK_R_SKIPPED      4  /* 1.0 if the last fused update predicated itself off */
 #define DPK_R_COMM_TIMEOUT 5  /* set to 1.0 (and left there) if one of the library's own
                                  all-reduce kernels gave up waiting for a peer rank:
-                                 the gradients of that step are not reduced */
+                                 the gradients of that step are not reduced, and every
+                                 later fused update is a no-op (state stays intact) */
 #define DPK_R_COUNT        8
 
 typedef struct dpk_handle dpk_handle;
@@ -134,7 +135,10 @@ int dpk_world_size(const dpk_handle* h);
  *   peer_grads    [world] this process's mapping of every rank's buffer
  *                 (peer_grads[rank] is the address given to dpk_bind),
  *   mc_signal     multicast address of a zero-initialised uint32[n_slots] array
- *                 that is symmetric too, local_signal its local address.
+ *                 that is symmetric too, local_signal its local address
+ *                 (n_slots >= 2; with >= 1024 slots the array also carries the
+ *                 per-range arrival counters dpk_reduce_update needs at W >= 4:
+ *                 65 536 slots serve any buffer size).
  * Needs a power-of-two world size (the average is taken as sum * 1/W).  No
  * reference counterpart beyond the DDP reducer both paths replace. */
 int dpk_bind_nvls(dpk_handle* h, void* mc_grads, void* const* peer_grads, void* mc_signal,
@@ -216,9 +220,16 @@ int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stre
  *       collective when the step is NVLink-bound.
  *   DPK_OPT_NORM_STAGING  1 = the norm pass stages its tiles through shared
  *       memory with TMA bulk copies (cp.async.bulk + mbarrier, 3 deep) instead of
- *       128-bit register loads.  Same partial sums, bit for bit. */
+ *       128-bit register loads.  Same partial sums, bit for bit.
+ *   DPK_OPT_PEER_TIMEOUT_MS  how long one of the library's own all-reduce kernels
+ *       waits for a peer rank before it gives up and raises DPK_R_COMM_TIMEOUT
+ *       (default 600 000 = ten minutes, the NCCL watchdog's default; the
+ *       environment variable DPK_PEER_TIMEOUT_MS sets the initial value).  After
+ *       a timeout the fused update leaves parameters, moments and EMA copies
+ *       untouched, so the caller can raise with the state intact. */
 #define DPK_OPT_OVERLAP_BLOCKS_PER_SM 1
 #define DPK_OPT_NORM_STAGING 2
+#define DPK_OPT_PEER_TIMEOUT_MS 3
 int dpk_set_option(dpk_handle* h, int32_t option, int64_t value);
 
 /* Two ranks only (after dpk_bind_nvls): gradient all-reduce AND the fused update
@@ -232,6 +243,22 @@ int dpk_set_option(dpk_handle* h, int32_t option, int64_t value);
  * the norm of the averaged gradient. */
 int dpk_reduce_update_pair(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
                            double inv_scale, void* stream);
+
+/* Any number of ranks >= 2 (after dpk_bind_nvls with a signal array of at least
+ * 1024 slots): the same replacement as dpk_reduce_update_pair -- DDP's bucketed
+ * all-reduce (utils/trainer.py:118-125) plus optimize() without clipping
+ * (:240-244) as ONE kernel.  Two ranks take the pair form.  Four or more: part of
+ * the grid reduces through the NVSwitch (multimem.ld_reduce, x 1/W, multimem.st:
+ * the arithmetic of the bucket all-reduce, so the averaged gradient is bit-identical
+ * and is what the gradient buffers hold afterwards) and publishes a per-range
+ * arrival counter; the rest of the grid runs the fused update, each thread waiting
+ * only for the range its vector lies in.  State afterwards is bit-identical to
+ * dpk_all_buckets_ready + dpk_wait_allreduce + dpk_fused_update(KEEP, no clip).
+ * If a peer stops arriving mid-kernel the step is abandoned where it stands and
+ * DPK_R_COMM_TIMEOUT is raised (parameters are then partly updated: restart from
+ * the last checkpoint); a peer that never shows up at all leaves the state intact. */
+int dpk_reduce_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
+                      double inv_scale, void* stream);
 
 /* Device address of the result block (DPK_R_COUNT doubles). */
 int dpk_result_ptr(dpk_handle* h, void** d_out);
@@ -285,8 +312,9 @@ int dpk_grad_norm_static(const void* d_grads, int64_t n, int32_t dtype, double i
 #define DPK_TIMING_SLOTS 256
 int dpk_timing_enable(dpk_handle* h, int32_t on);
 /* Waits for the recorded events, writes up to `cap` durations (ms, oldest
- * first) for kernel `which` (0 = fused update, 1 = sum-of-squares) and clears
- * them. */
+ * first) for kernel `which` (0 = fused update, or the fused all-reduce + update
+ * kernel; 1 = sum-of-squares; 2 = one bucket's all-reduce on the communication
+ * stream) and clears them. */
 int dpk_timing_read_sync(dpk_handle* h, int32_t which, float* ms_out, int32_t cap, int32_t* n_out);
 /* Kernels this handle has launched since creation. */
 int dpk_launch_count(const dpk_handle* h, int64_t* out);
@@ -295,8 +323,11 @@ int dpk_launch_count(const dpk_handle* h, int64_t* out);
  * patterns v (all 2^32) for which the reciprocal-and-correct division of
  * sqrt(v) -- the only dividends the kernel has -- by `divisor` differs from
  * div.rn; d_out2[1] = number of bf16 bit patterns whose
- * approximate square root rounds to a different bf16 than sqrt.rn's.  Both must
- * be 0.  d_out2: two device uint64. */
+ * approximate square root rounds to a different bf16 than sqrt.rn's, plus the
+ * number of fp32 bit patterns (all 2^32) the kernel's packed fp32->bf16 rounding
+ * converts differently from cvt.rn.bf16.f32, plus the number of bf16 patterns its
+ * bf16->fp32 unpacking does not reproduce exactly.  Both must be 0.
+ * d_out2: two device uint64. */
 int dpk_selftest_arith(double divisor, unsigned long long* d_out2, void* stream);
 
 /* ---- loss-aware timestep sampler.  Absent from the reference;

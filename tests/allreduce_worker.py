@@ -1,0 +1,120 @@
+"""Worker for tests/test_gpu_multi.py: one rank of a W-rank NCCL job on real GPUs (W = 2, 4 or 8).
+
+* bench.parity_check: the library's all-reduce for this world size (pair exchange at W=2, NVSwitch multimem at
+  W>=4, or -- with DPK_FORCE_MULTIMEM=1 -- the switch kernels at W=2 too) against ncclAvg and against the
+  float64 mean rounded once; the one-kernel all-reduce + update against all-reduce-then-update (bit-identical)
+  and against torch.optim.AdamW + eager EMA.
+* the same state against the reference port (oracle/torch_port.py) driven with ncclAvg gradients.
+* a second pass with few collective blocks and small units, so that every collective block walks many units
+  and update blocks wait on many different arrival counters.
+* the loss-aware sampler's packed all-gather: rank-major order, ragged and empty local batches, bit-exact
+  history / counts / weights against the numpy restatement.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import bench  # noqa: E402
+from distributed_pipeline_b200 import FusedAdamW, _lib  # noqa: E402
+from distributed_pipeline_b200.sampler import LossSecondMomentResampler  # noqa: E402
+from oracle.sampler_oracle import LossSecondMomentResamplerOracle  # noqa: E402
+from oracle.torch_port import ReferenceUpdatePort  # noqa: E402
+
+
+def port_check(world, rank, dev, dtype):
+    """Three steps of the library (selected all-reduce + fused update, clip 1.0) against the reference port fed
+    with ncclAvg gradients.  fp32: relative 1e-6 (W>=4: summation order differs from NCCL's by design);
+    bf16: one bf16 ulp at W=2 (same gradients bit for bit), a few at W>=4 where the switch rounds differently."""
+    shapes = [(257, 33), (7,), (150001,), (64, 64), (3,)]
+    torch.manual_seed(11)
+    ps = [torch.nn.Parameter((torch.randn(s, device=dev) * 0.02).to(dtype)) for s in shapes]
+    ref_ps = [torch.nn.Parameter(p.detach().clone()) for p in ps]
+    opt = FusedAdamW(ps, lr=1e-3, weight_decay=0.01, ema_rates=[0.999], bucket_cap_mb=0.25,
+                     grad_mode=_lib.GRAD_CLIPPED, symmetric_grads=True)
+    opt.engine.init_comm()
+    opt.engine.enable_nvls(opt.flat.grads)
+    port = ReferenceUpdatePort(ref_ps, lr=1e-3, ema_rates=[0.999], weight_decay=0.01, gradient_clipping=1.0)
+    gen = torch.Generator(device=dev).manual_seed(900 + rank)
+    for _ in range(3):
+        g = (torch.randn(opt.flat.layout.n_elems, device=dev, generator=gen) * 0.05).to(dtype)
+        opt.flat.grads.copy_(g)
+        avg = g.clone()
+        dist.all_reduce(avg, op=dist.ReduceOp.AVG)
+        for p, gv in zip(ref_ps, opt.flat.layout.views(avg, opt.flat.shapes)):
+            p.grad = gv.clone()
+        opt.reduce_and_step(1.0)
+        port.optimize()
+    torch.cuda.synchronize()
+    worst = 0.0
+    for a, b in list(zip(ps, ref_ps)) + list(zip(opt.flat.ema_views[0], port.ema_params[0])):
+        a, b = a.detach().double(), b.detach().double()
+        rms = b.pow(2).mean().sqrt()
+        worst = max(worst, float(((a - b).abs() / (b.abs() + rms)).max().item()))
+    tol = 1e-6 if dtype == torch.float32 else (2 ** -7 if world == 2 else 2 ** -5)
+    assert worst <= tol, f"{dtype} W={world}: parameters/EMA differ from the reference port by {worst:.3e} (> {tol:.1e})"
+    opt.engine.close()
+    return worst
+
+
+def sampler_check(world, rank, dev):
+    T = 50
+    holder = FusedAdamW([torch.nn.Parameter(torch.zeros(1024, device=dev))], ema_rates=[])
+    holder.engine.init_comm()
+    sampler = LossSecondMomentResampler(T, history_per_term=4, device=dev, engine=holder.engine, max_local_batch=16)
+    ref = LossSecondMomentResamplerOracle(T, 4)
+    rng = np.random.RandomState(7)                         # same stream on every rank: all ranks know all inputs
+    for _ in range(40):
+        sizes = [int(rng.randint(0, 17)) for _ in range(world)]   # ragged, possibly empty, per rank
+        ts = [rng.randint(0, T, size=s) for s in sizes]
+        ls = [(rng.rand(s) + 0.1).astype(np.float32) for s in sizes]
+        sampler.update_with_local_losses(torch.from_numpy(ts[rank]).to(dev), torch.from_numpy(ls[rank]).to(dev))
+        ref.update_with_gathered(ts, ls)
+    hist, counts = sampler.state()
+    assert np.array_equal(counts.cpu().numpy().astype(np.int64), ref._loss_counts)
+    assert np.array_equal(hist.cpu().numpy().view(np.uint64), ref._loss_history.view(np.uint64))
+    assert np.array_equal(sampler.weights().view(np.uint64), ref.weights().view(np.uint64))
+    np.random.seed(5)
+    a = sampler.sample(32, dev)[0].cpu().numpy()
+    np.random.seed(5)
+    b = ref.sample(32)[0]
+    assert np.array_equal(a, np.asarray(b)), "sampled timesteps differ for the same RNG state"
+    sampler.close()
+    holder.engine.close()
+
+
+def main():
+    tmp = sys.argv[1]
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    rep = bench.parity_check(world, rank, dev, use_nvls=True)
+    if rank == 0:
+        print("parity_check", rep, flush=True)
+    assert rep["ok"], rep
+    # few collective blocks, small units: every block walks many units
+    os.environ["DPK_FUSED_COMM_BLOCKS"] = "3"
+    os.environ["DPK_FUSED_UNIT_KB"] = "64"
+    rep2 = bench.parity_check(world, rank, dev, use_nvls=True)
+    assert rep2["ok"], rep2
+    del os.environ["DPK_FUSED_COMM_BLOCKS"], os.environ["DPK_FUSED_UNIT_KB"]
+    for dtype in (torch.float32, torch.bfloat16):
+        w = port_check(world, rank, dev, dtype)
+        if rank == 0:
+            print(f"reference port, {dtype}, W={world}: worst relative difference {w:.3e}", flush=True)
+    sampler_check(world, rank, dev)
+    dist.barrier()
+    if rank == 0:
+        open(os.path.join(tmp, "allreduce_ok"), "w").write("ok")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

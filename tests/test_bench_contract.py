@@ -27,8 +27,46 @@ def test_reference_arm_prints_contract_line():
     assert d["config"]["bytes_per_param"] == 48
 
 
-def test_non_zero_ranks_of_the_reference_arm_do_nothing():
-    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
-    proc = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
-                          capture_output=True, text=True, timeout=120, env=env, cwd=ROOT)
-    assert proc.returncode == 0 and proc.stdout.strip() == ""
+def test_reference_arm_runs_on_every_rank_over_gloo():
+    """N>1: the reference arm is launched like the GPU arm (torchrun); every rank runs the port with DDP's
+    pre-scale + bucketed all-reduce over gloo in front, threads = physical cores // W, rank 0 prints the line."""
+    sys.path.insert(0, ROOT)
+    from distributed_pipeline_b200.dist_util import find_free_port
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    proc = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                           "--master-addr", "127.0.0.1", "--master-port", str(find_free_port()),
+                           os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--workload",
+                           "toy-fp32-ema2-clip", "--steps", "3", "--warmup", "1"],
+                          capture_output=True, text=True, timeout=300, env=env, cwd=ROOT)
+    assert proc.returncode == 0, proc.stderr[-2000:]
+    lines = [l for l in proc.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["config"]["world_size"] == 2
+    assert d["config"]["host_threads_per_rank"] == max(1, d["config"]["physical_cores"] // 2)
+    assert d["cpu_baseline"]["cores"] == 2 * d["config"]["host_threads_per_rank"]
+    assert "gloo" in d["config"]["allreduce"] and d["value"] > 0
+
+
+def test_ddp_style_allreduce_is_what_torch_ddp_computes():
+    """bench.py's stand-in for the DDP reducer in the reference arm: pre-multiply by 1/W, SUM, in buckets."""
+    import torch
+    sys.path.insert(0, ROOT)
+    import bench
+
+    class FakeDist:
+        class ReduceOp:
+            SUM = "sum"
+        calls = []
+
+        @staticmethod
+        def all_reduce(t, op=None):
+            FakeDist.calls.append(t.numel())
+            t.mul_(3)          # three identical ranks: SUM of three pre-scaled copies
+
+    gs = [torch.randn(5, 7), torch.randn(3), torch.randn(11)]
+    want = [g.clone() * (1.0 / 3) * 3 for g in gs]
+    bench.ddp_style_allreduce(gs, 3, FakeDist, cap_bytes=50)
+    for a, b in zip(gs, want):
+        assert torch.allclose(a, b, rtol=1e-6)
+    assert FakeDist.calls == [14, 35]      # last tensors first; a bucket closes once it reaches the cap
