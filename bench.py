@@ -362,14 +362,15 @@ def parity_check(world, rank, dev, use_nvls, verbose=False):
                 o.engine.enable_nvls(o.flat.grads)
             return o
         fused, staged = make(), make()
-        report["path"] = ("pair exchange" if world == 2 else "NVSwitch multimem") if staged.engine.nvls else "ncclAllReduce"
+        forced = os.environ.get("DPK_FORCE_MULTIMEM") == "1"
+        report["path"] = ("pair exchange" if world == 2 and not forced else "NVSwitch multimem") if staged.engine.nvls else "ncclAllReduce"
         # the torch side: same initial parameters, stock AdamW, eager EMA
         ref_p = [torch.nn.Parameter(p.detach().clone()) for p in staged.flat.param_list]
         ref_opt = torch.optim.AdamW(ref_p, lr=1e-3, weight_decay=0.01, foreach=True)
         ref_ema = [[p.detach().clone() for p in ref_p] for _ in rates]
         gen = torch.Generator(device=dev).manual_seed(100 + rank)
         ar = {"elements": 0, "off_rounded_mean": 0, "nccl_off_rounded_mean": 0, "bit_equal_ncclavg": True,
-              "max_abs_diff_vs_ncclavg": 0.0, "max_err_in_ulp_of_largest_addend": 0.0}
+              "max_abs_diff_vs_ncclavg": 0.0, "max_err_in_spacings_of_largest_addend": 0.0}
         up = {"fused_equals_staged": True, "max_rel_err_vs_torch_adamw": 0.0, "max_ulp_vs_torch_adamw": 0,
               "logged_norm_rel_err": 0.0}
         n = staged.flat.layout.n_elems
@@ -397,13 +398,16 @@ def parity_check(world, rank, dev, use_nvls, verbose=False):
             torch.cuda.synchronize()
             ours = staged.flat.grads.clone()
             err = (ours.double() - mean64).abs()
-            ulp_big = torch.maximum(biggest, torch.tensor(1e-30, device=dev)).double() * (2.0 ** -24 if dtype == torch.float32 else 2.0 ** -8)
+            # spacing of the dtype at the magnitude of the largest addend: 2^(floor(log2|x|) - mantissa bits)
+            mant = 23 if dtype == torch.float32 else 7
+            ulp_big = torch.exp2(torch.floor(torch.log2(torch.clamp(biggest.double(), min=1e-30))) - mant)
             ar["elements"] += n
             ar["off_rounded_mean"] += int((ours != exact).sum().item())
             ar["nccl_off_rounded_mean"] += int((nccl != exact).sum().item())
             ar["bit_equal_ncclavg"] = ar["bit_equal_ncclavg"] and bool(torch.equal(ours, nccl))
             ar["max_abs_diff_vs_ncclavg"] = max(ar["max_abs_diff_vs_ncclavg"], float((ours.float() - nccl.float()).abs().max().item()))
-            ar["max_err_in_ulp_of_largest_addend"] = max(ar["max_err_in_ulp_of_largest_addend"], float((err / ulp_big).max().item()))
+            ar["max_err_in_spacings_of_largest_addend"] = max(ar["max_err_in_spacings_of_largest_addend"],
+                                                              float((err / ulp_big).max().item()))
             # replicas agree
             chk = ours.clone()
             dist.broadcast(chk, 0)
@@ -440,17 +444,21 @@ def parity_check(world, rank, dev, use_nvls, verbose=False):
             up["max_rel_err_vs_torch_adamw"] = max(up["max_rel_err_vs_torch_adamw"], float(rel))
             up["max_ulp_vs_torch_adamw"] = max(up["max_ulp_vs_torch_adamw"],
                                                int((_ordered_bits(a.contiguous()) - _ordered_bits(b.contiguous())).abs().max().item()))
-        # verdicts
+        # verdicts.  `switch`: the NVSwitch did the additions (multimem.ld_reduce); its fp32 sums have
+        # so far always come out as the correctly rounded mean (reported, and asserted in tests/), its
+        # bf16 sums are NOT single IEEE roundings (measured: up to one bf16 spacing of the largest
+        # addend away from the exact mean) -- so the gate for that path is an absolute one that a
+        # missing or doubled contribution would still break by orders of magnitude.
+        switch = staged.engine.nvls and (world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1")
+        if switch:
+            ar_ok = ar["max_err_in_spacings_of_largest_addend"] <= (1.0 if dtype == torch.float32 else 2.0)
+        else:
+            ar_ok = ar["bit_equal_ncclavg"]          # pair exchange / ncclAllReduce itself: one rounding of (a+b)/2, or NCCL's own bits
+            if staged.engine.nvls:
+                ar_ok = ar_ok and ar["off_rounded_mean"] == 0
         if dtype == torch.float32:
-            ar_ok = ar["off_rounded_mean"] == 0 if staged.engine.nvls else ar["bit_equal_ncclavg"]
-            if world == 2:
-                ar_ok = ar_ok and ar["bit_equal_ncclavg"]
             up_ok = up["fused_equals_staged"] and up["max_rel_err_vs_torch_adamw"] <= 1e-6 and up["logged_norm_rel_err"] <= 1e-5
         else:
-            if world == 2 or not staged.engine.nvls:
-                ar_ok = ar["bit_equal_ncclavg"]
-            else:
-                ar_ok = ar["max_err_in_ulp_of_largest_addend"] <= 1.0
             up_ok = up["fused_equals_staged"] and up["max_ulp_vs_torch_adamw"] <= 1 and up["logged_norm_rel_err"] <= 2 ** -7
         ar["ok"], up["ok"] = bool(ar_ok), bool(up_ok)
         ok = ok and ar_ok and up_ok
@@ -465,9 +473,11 @@ def parity_check(world, rank, dev, use_nvls, verbose=False):
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     report["ok"] = bool(flag.item())
     report["max_ulp"] = worst_ulp
-    report["tolerances"] = ("fp32: all-reduce = correctly rounded mean (0 elements off), bit-equal ncclAvg at W=2; update "
-                            "rel 1e-6 vs torch AdamW+EMA, fused == staged bit for bit; bf16: bit-equal ncclAvg at W=2, "
-                            "else within one bf16 ulp of the largest addend; update within 1 bf16 ulp")
+    report["tolerances"] = ("all-reduce: W=2 pair exchange / NCCL bit-equal to ncclAvg (= the correctly rounded mean); through "
+                            "the NVSwitch |ours - float64 mean| <= 1 fp32 / 2 bf16 spacings of the largest addend "
+                            "(off_rounded_mean reports how many elements are not the rounded mean: 0 expected in fp32); "
+                            "update: one-kernel form bit-identical to all-reduce-then-update, and vs torch AdamW + eager EMA "
+                            "on the same averaged gradient rel 1e-6 (fp32) / 1 ulp (bf16); logged norm 1e-5 / 2^-7")
     return report
 
 
@@ -603,7 +613,8 @@ def run_ours(args):
             traffic = json.load(f).get(f"{args.workload}:{args.grad_mode}")
     kname = "fused_update_kernel"
     if one_kernel:
-        kname = "fused_update_kernel<kGradPair> (all-reduce inside)" if world == 2 else "reduce_update_kernel (all-reduce inside)"
+        pair = world == 2 and os.environ.get("DPK_FORCE_MULTIMEM") != "1"
+        kname = "fused_update_kernel<kGradPair> (all-reduce inside)" if pair else "reduce_update_kernel (all-reduce inside)"
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_avg": k_ms, "kernel_ms_min": min(kernel_ms) if kernel_ms else None,
@@ -629,14 +640,15 @@ def run_ours(args):
             per = [sum(comm_ms[i:i + n_buckets]) for i in range(0, len(comm_ms) - n_buckets + 1, n_buckets)]
             c_ms = sum(per) / len(per) if per else float("nan")
             c_n = len(per)
-            c_kernel = (("pair_allreduce_kernel" if world == 2 else "nvls_allreduce_kernel") if eng.nvls
+            pair = world == 2 and os.environ.get("DPK_FORCE_MULTIMEM") != "1"
+            c_kernel = (("pair_allreduce_kernel" if pair else "nvls_allreduce_kernel") if eng.nvls
                         else "ncclAllReduce") + f" x {n_buckets} buckets (sum of their durations)"
         algbw = S / (c_ms * 1e-3) / 1e9
         busbw = algbw * 2 * (world - 1) / world
         # bytes that must cross each GPU's links, per direction: the pair forms move S/2 out and back (one-kernel
         # pair: S in); the switch forms S(1 + 1/W); a ring 2(W-1)/W * S
         if eng.nvls:
-            wire = S * (1.0 if world == 2 else 1.0 + 1.0 / world)
+            wire = S * (1.0 if (world == 2 and os.environ.get("DPK_FORCE_MULTIMEM") != "1") else 1.0 + 1.0 / world)
         else:
             wire = S * 2 * (world - 1) / world
         roofline_comm = {"bound": "nvlink", "kernel": c_kernel, "kernel_ms_avg": c_ms, "launches_timed": c_n,

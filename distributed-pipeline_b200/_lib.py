@@ -16,7 +16,7 @@ import threading
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libdpk.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 F32, BF16 = 0, 1
 MAX_EMA = 4
 GRAD_KEEP, GRAD_CLIPPED, GRAD_ZERO = 0, 1, 2
@@ -51,6 +51,7 @@ class Config(C.Structure):
         ("eps", C.c_double),
         ("bucket_cap_bytes", C.c_int64),
         ("edge_bucket_bytes", C.c_int64),
+        ("seg_frozen", C.POINTER(C.c_int32)),
     ]
 
 

@@ -403,7 +403,7 @@ int dpk_create(dpk_handle** out, const dpk_config* cfg) {
       Tile t;
       t.start = h->seg_off[s] + pos;
       t.len = (int)std::min<long long>(tile_elems, h->seg_len[s] - pos);
-      t.seg = s;
+      t.seg = s | ((cfg->seg_frozen && cfg->seg_frozen[s]) ? kTileFrozen : 0);
       h->tiles.push_back(t);
     }
   }

@@ -25,8 +25,9 @@ constexpr int kThreads = 256;
 struct Tile {
   long long start;  // element offset in the flat buffers (multiple of 16 bytes)
   int len;          // elements in this tile (<= tile_elems)
-  int seg;          // parameter tensor it belongs to
+  int seg;          // parameter tensor it belongs to; kTileFrozen set if that tensor takes no optimizer step
 };
+constexpr int kTileFrozen = 1 << 30;
 
 struct alignas(8) TilePartial {
   float sumsq;
@@ -413,7 +414,8 @@ sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int 
   for (int t = tile_begin + blockIdx.x; t < tile_end; t += gridDim.x) {
     const Tile tile = tiles[t];
     float acc = 0.f, nonfin = 0.f;
-    tile_sumsq<T, U>(g + tile.start, tile.len, inv_scale, false, acc, nonfin);
+    // a tensor without a gradient is not part of the norm (clip_grad_norm_ skips grad=None)
+    if (!(tile.seg & kTileFrozen)) tile_sumsq<T, U>(g + tile.start, tile.len, inv_scale, false, acc, nonfin);
     const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
     const int any_bad = __syncthreads_or((int)bad);
     const float s = block_sum(acc, red);
@@ -482,7 +484,7 @@ sumsq_tiles_tma_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, 
       asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
                    : "=r"(done) : "r"(bar), "r"(parity) : "memory");
     }
-    const int len = desc[s].len;
+    const int len = (desc[s].seg & kTileFrozen) ? 0 : desc[s].len;
     float acc = 0.f, nonfin = 0.f;
     tile_sumsq<T, U, true>(reinterpret_cast<const T*>(stage_mem + (size_t)s * tile_bytes_max), len, inv_scale, false,
                            acc, nonfin);
@@ -655,9 +657,13 @@ struct UpdateArgs {
 
 // Returns true only in kGradFlagged mode, when the wait for a peer was abandoned
 // (nothing has been stored for this vector then).
+// `frozen`: the tensor has no gradient (requires_grad=False): torch.optim.AdamW
+// skips it entirely -- no decay, no moments, no step (optim/adam.py:232-238 collects
+// only params with a grad) -- while update_ema (utils/trainer.py:360-370) still
+// walks every parameter.  Its gradient bytes are not read as data.
 template <typename T, int K, int GM, bool FULL>
 __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long long vidx, int rem,
-                                              float coef, float& acc) {
+                                              float coef, float& acc, bool frozen) {
   using Tr = ElemTraits<T>;
   uint4* pv = reinterpret_cast<uint4*>(a.p) + vidx;
   uint4* gv = reinterpret_cast<uint4*>(a.g) + vidx;
@@ -709,6 +715,7 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
     Tr::unpack4(rp, c, p);
     Tr::unpack4(rm, c, m);
     Tr::unpack4(rv, c, v);
+    if (!frozen) {
     // Each block below is one torch kernel: compute in fp32, then the store to the
     // state dtype (rnd4*: nothing for fp32, round-to-nearest-even for bf16).
     // grad.mul_(1/2^lg) (upstream loss-scale) and _foreach_mul_(grads, coef): a
@@ -760,6 +767,7 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
 #pragma unroll
     for (int j = 0; j < 4; ++j) p[j] = __fmaf_rn(s.neg_step, __fdiv_rn(m[j], d[j]), p[j]);
     Tr::rnd4_store(p, wp, c);
+    }  // !frozen
 
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -842,13 +850,14 @@ __device__ __forceinline__ void update_chunks(const UpdateArgs<T, K>& a, int wor
     len = len > a.chunk_elems ? a.chunk_elems : len;
     const long long vbase = (tile.start + off) / VE;
     const int nfull = len > 0 ? len / VE : 0;       // vectors with every lane valid
+    const bool frozen = (tile.seg & kTileFrozen) != 0;
     float acc = 0.f;
     bool aborted = false;
     const int v = threadIdx.x;
     if (v < nfull)
-      aborted = update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
+      aborted = update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc, frozen);
     else if (v == nfull && len > nfull * VE)        // ragged end of a tensor: one masked vector
-      aborted = update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc);
+      aborted = update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc, frozen);
 
     // block sum, fixed order, one barrier per item (the exchange buffer alternates)
 #pragma unroll

@@ -39,7 +39,9 @@ def setup_dist(backend=None, silent=False) -> bool:
     if _state["setup_done"] is not None:
         return _state["setup_done"]
     result = False
-    if is_available() and os.environ.get("LOCAL_RANK") is not None and os.environ.get("WORLD_SIZE") is not None:
+    # the reference's condition (basic_utils/dist_util.py:66): LOCAL_RANK alone decides; an environment
+    # that lacks the other env:// variables fails inside init_process_group and falls back below
+    if is_available() and os.environ.get("LOCAL_RANK") is not None:
         try:
             if backend is None:
                 backend = "nccl" if torch.cuda.is_available() else "gloo"

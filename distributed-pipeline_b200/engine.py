@@ -32,7 +32,10 @@ class _DeviceArray:
 class Engine:
     def __init__(self, layout: FlatLayout, dtype: torch.dtype, device: torch.device,
                  ema_rates: Sequence[float] = (), betas=(0.9, 0.999), eps: float = 1e-8,
-                 bucket_cap_bytes: int = 128 << 20, tile_elems: int = 0, edge_bucket_bytes: int = 0):
+                 bucket_cap_bytes: int = 128 << 20, tile_elems: int = 0, edge_bucket_bytes: int = 0,
+                 frozen: Optional[Sequence[bool]] = None):
+        """``frozen[i]``: tensor i has no gradient (``requires_grad=False``): no AdamW step, not part
+        of the norm, EMA copies still advanced (what torch.optim.AdamW and update_ema do)."""
         device = torch.device(device)
         if device.type != "cuda":
             raise RuntimeError(
@@ -53,13 +56,17 @@ class Engine:
         offs = (C.c_int64 * max(n_seg, 1))(*layout.offsets)
         nums = (C.c_int64 * max(n_seg, 1))(*layout.numels)
         rates = (C.c_double * max(len(self.ema_rates), 1))(*self.ema_rates)
+        self.frozen = [bool(f) for f in frozen] if frozen is not None else [False] * n_seg
+        if len(self.frozen) != n_seg:
+            raise ValueError("frozen: one flag per tensor")
+        frozen_arr = (C.c_int32 * max(n_seg, 1))(*[int(f) for f in self.frozen]) if any(self.frozen) else None
         cfg = _lib.Config(
             abi_version=_lib.ABI_VERSION, dtype=dtype_code(dtype),
             device=device.index,
             n_segments=n_seg, n_ema=len(self.ema_rates), tile_elems=tile_elems, n_elems=layout.n_elems,
             seg_offsets=offs, seg_numel=nums, ema_rates=rates,
             beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, bucket_cap_bytes=bucket_cap_bytes,
-            edge_bucket_bytes=edge_bucket_bytes)
+            edge_bucket_bytes=edge_bucket_bytes, seg_frozen=frozen_arr)
         _lib.check(self.lib.dpk_create(C.byref(self._h), C.byref(cfg)))
         self._bound: List[torch.Tensor] = []
         self.world_size = 1
@@ -137,6 +144,34 @@ class Engine:
         _lib.check(self.lib.dpk_bind_nvls(self._h, mc_grads, peers, mc_sig, sig.data_ptr(), n_slots))
         self._nvls = (hdl, hsig, sig)  # keep the mappings alive
         self.nvls = True
+
+    def enable_nvls_agreed(self, flat, group=None, n_slots: int = 65536):
+        """Switch the gradient all-reduce to the library's symmetric-memory kernels only if EVERY
+        rank can: the decision is taken collectively (MIN over ranks before and after the set-up),
+        because a rank that quietly stayed on NCCL while its peers spin in the symmetric-memory
+        kernels would hang the job.  Returns (enabled, reason-if-not).  Collective."""
+        import torch.distributed as dist
+        group = group if group is not None else dist.group.WORLD
+
+        def all_ok(flag: bool) -> bool:
+            t = torch.tensor([1 if flag else 0], device=self.device, dtype=torch.int32)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+            return bool(t.item())
+
+        why = None
+        if not flat.symmetric:
+            why = f"symmetric allocation failed on this rank: {flat.symmetric_error}"
+        if not all_ok(flat.symmetric):
+            return False, why or "symmetric allocation failed on another rank"
+        # every rank holds symmetric memory: the rendezvous below is entered by all of them
+        try:
+            self.enable_nvls(flat.grads, group=group, n_slots=n_slots)
+        except Exception as exc:  # no multicast support, mapping failure, ...
+            why = str(exc)
+        if not all_ok(self.nvls):
+            self.nvls = False
+            return False, why or "symmetric-memory set-up failed on another rank"
+        return True, None
 
     @property
     def buckets(self) -> List[Tuple[int, int]]:

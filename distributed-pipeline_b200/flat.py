@@ -47,8 +47,11 @@ class FlatLayout:
         return [flat[o:o + n].view(s) for o, n, s in zip(self.offsets, self.numels, shapes)]
 
     def segment_of(self, start: int, count: int) -> List[int]:
-        """Indices of the tensors that begin inside flat range [start, start+count)."""
-        return [i for i, o in enumerate(self.offsets) if start <= o < start + count]
+        """Indices of the tensors that begin inside flat range [start, start+count).  A trailing
+        empty tensor sits at offset == n_elems: it belongs to the range that ends there."""
+        end = start + count
+        return [i for i, o in enumerate(self.offsets)
+                if start <= o < end or (o == end == self.n_elems and self.numels[i] == 0)]
 
 
 _DTYPES = {torch.float32: 0, torch.bfloat16: 1}
@@ -85,6 +88,7 @@ class FlatState:
             if p.device != self.device or p.dtype != self.dtype:
                 raise TypeError("all parameters must share one device and dtype")
         self.shapes = [p.shape for p in self.param_list]
+        self.frozen = [not p.requires_grad for p in self.param_list]
         self.layout = FlatLayout.from_numels([p.numel() for p in self.param_list], first.element_size())
         n = self.layout.n_elems
 
@@ -120,7 +124,8 @@ class FlatState:
                 if p.grad is not None:
                     gv.copy_(p.grad)
                 p.data = pv
-                p.grad = gv
+                # a frozen parameter keeps grad=None, as in torch (the optimizer and the norm skip it)
+                p.grad = gv if p.requires_grad else None
             # EMA copies start as copies of the parameters (utils/trainer.py:111-113)
             for e in self.emas:
                 e.copy_(self.params)
@@ -130,6 +135,8 @@ class FlatState:
         for p, pv, gv in zip(self.param_list, self.param_views, self.grad_views):
             if p.data_ptr() != pv.data_ptr():
                 raise RuntimeError("a parameter no longer aliases the flat buffer")
+            if not p.requires_grad:
+                continue
             if p.grad is None or p.grad.data_ptr() != gv.data_ptr():
                 raise RuntimeError(
                     "a gradient no longer aliases the flat buffer (was it set to None?); "

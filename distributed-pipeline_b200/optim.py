@@ -25,7 +25,8 @@ class FusedAdamW:
         params = list(params)
         self.flat = FlatState(params, n_ema=len(ema_rates), symmetric_grads=symmetric_grads)
         self.engine = Engine(self.flat.layout, self.flat.dtype, self.flat.device, ema_rates, betas, eps,
-                             bucket_cap_bytes=int(bucket_cap_mb * 1024 * 1024), tile_elems=tile_elems)
+                             bucket_cap_bytes=int(bucket_cap_mb * 1024 * 1024), tile_elems=tile_elems,
+                             frozen=self.flat.frozen)
         f = self.flat
         self.engine.bind(f.params, f.grads, f.exp_avg, f.exp_avg_sq, f.emas)
         self.defaults = dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay, amsgrad=False,
@@ -178,13 +179,15 @@ class FusedAdamW:
             return {}
         f = self.flat
         return {p: {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
-                for p, m, v in zip(f.param_list, f.exp_avg_views, f.exp_avg_sq_views)}
+                for p, m, v, fr in zip(f.param_list, f.exp_avg_views, f.exp_avg_sq_views, f.frozen) if not fr}
 
     def state_dict(self) -> Dict:
         f = self.flat
         state = {}
         if self.step_count:
             for i, (m, v) in enumerate(zip(f.exp_avg_views, f.exp_avg_sq_views)):
+                if f.frozen[i]:
+                    continue  # torch.optim.AdamW keeps no state for a parameter that never had a gradient
                 state[i] = {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
         groups = []
         for g in self.param_groups:
@@ -210,7 +213,13 @@ class FusedAdamW:
             return
         steps = set()
         for i, (m, v) in enumerate(zip(f.exp_avg_views, f.exp_avg_sq_views)):
-            st = state[i] if i in state else state[str(i)]
+            st = state.get(i, state.get(str(i)))
+            if st is None:
+                # no entry: torch never stepped this parameter (frozen / never received a gradient)
+                if not f.frozen[i]:
+                    m.zero_()
+                    v.zero_()
+                continue
             m.copy_(st["exp_avg"])
             v.copy_(st["exp_avg_sq"])
             steps.add(int(float(st["step"])))

@@ -44,8 +44,11 @@ class BucketReducer:
         missing = set(range(len(flat.param_list))) - set(self.param_bucket)
         if missing:
             raise RuntimeError(f"bucket plan does not cover parameters {sorted(missing)[:5]}...")
-        self._pending = [len(idxs) for idxs in self.bucket_params]
-        self._ready = [False] * len(ranges)
+        # only parameters that will receive a gradient (and so fire a hook) are waited for;
+        # a bucket of frozen tensors only is ready from the start
+        self._hooked = [sum(1 for i in idxs if flat.param_list[i].requires_grad) for idxs in self.bucket_params]
+        self._pending = list(self._hooked)
+        self._ready = [n == 0 for n in self._hooked]
         self._next = 0
         self._handles = []
         for i, p in enumerate(flat.param_list):
@@ -86,8 +89,8 @@ class BucketReducer:
             for b in range(self._next, len(self._ready)):
                 self.engine.bucket_ready(b)
             self.engine.wait_allreduce()
-        self._pending = [len(idxs) for idxs in self.bucket_params]
-        self._ready = [False] * len(self._ready)
+        self._pending = list(self._hooked)
+        self._ready = [n == 0 for n in self._hooked]
         self._next = 0
         self._callback_queued = False
         self.armed = False

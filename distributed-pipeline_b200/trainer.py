@@ -154,14 +154,12 @@ class TrainLoop:
                 # the gradient all-reduce runs on the library's own kernels over
                 # symmetric memory; NCCL stays the path when the NVSwitch multicast
                 # mapping cannot be set up (and "nvls" was not demanded)
-                try:
-                    if not self.opt.flat.symmetric:
-                        raise RuntimeError(f"symmetric allocation failed: {self.opt.flat.symmetric_error}")
-                    self.opt.engine.enable_nvls(self.opt.flat.grads)
-                except Exception as exc:
+                # (decided by all ranks together: see Engine.enable_nvls_agreed)
+                enabled, why = self.opt.engine.enable_nvls_agreed(self.opt.flat)
+                if not enabled:
                     if grad_allreduce == "nvls":
-                        raise
-                    self.logger.log(f"symmetric-memory all-reduce unavailable ({exc}); using NCCL")
+                        raise RuntimeError(f"grad_allreduce='nvls' was demanded but is unavailable: {why}")
+                    self.logger.log(f"symmetric-memory all-reduce unavailable ({why}); using NCCL")
             self._reducer = BucketReducer(self.opt.flat, self.opt.engine)
             self.ddp_model = FlatDDP(self.model, self._reducer)
             # Two ranks, nobody needs the averaged gradient afterwards, no clipping: the
@@ -186,6 +184,9 @@ class TrainLoop:
                            for _ in range(16)]
         self._norm_ring_pos = 0
         self._grads_are_zero = True  # fresh buffer
+        # any forward that records a graph may be followed by a backward, whoever calls it (a subclass
+        # with its own forward_backward included): from then on the buffer is no longer known to be zero
+        self.model.register_forward_pre_hook(self._mark_grads_dirty)
         torch.cuda.empty_cache()
 
     # ---- resume (reference :136-173) -----------------------------------------
@@ -261,6 +262,10 @@ class TrainLoop:
         self.optimize()
         self.log_step()
 
+    def _mark_grads_dirty(self, *_):
+        if torch.is_grad_enabled():
+            self._grads_are_zero = False
+
     def _zero_grad(self):
         # reference :203-207 zeroes 209 tensors one by one; one fill here, and
         # none at all when the fused pass already left the buffer zeroed.
@@ -304,6 +309,8 @@ class TrainLoop:
     # ---- the update (reference :237-275) -------------------------------------
     def optimize(self):
         self._drain_norms(block=False)
+        # a flag left over from a direct opt.step() nobody consumed must not swallow this step's EMA
+        self.opt.ema_done = [False] * len(self.opt.ema_done)
         if self.use_fp16:
             return self._optimize_fp16()
         if self._pair_fused and self.gradient_clipping > 0:
@@ -385,8 +392,8 @@ class TrainLoop:
         self.logger.logkv_mean("grad_norm", res[_lib.R_TOTAL_NORM])
 
     def _after_fused_step(self):
-        if self.opt.grad_mode == _lib.GRAD_ZERO:
-            self._grads_are_zero = True
+        # known here and only here: the fused pass either zeroed the buffer or it did not
+        self._grads_are_zero = self.opt.grad_mode == _lib.GRAD_ZERO
         if not self._norm_requested:
             return
         self._norm_requested = False

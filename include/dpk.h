@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define DPK_ABI_VERSION 1
+#define DPK_ABI_VERSION 2
 
 /* error codes (<0); >0 is a cudaError_t */
 #define DPK_E_BADARG  (-1)  /* null / misaligned / out-of-range argument      */
@@ -93,6 +93,12 @@ typedef struct dpk_config {
                                 does the same for its first bucket.  0 = cap/8;
                                 >= cap: plain cap-sized buckets.  Results do not
                                 depend on the bucket plan. */
+  const int32_t* seg_frozen; /* [n_segments] or NULL: non-zero = this tensor has no
+                                gradient (requires_grad=False).  As with
+                                torch.optim.AdamW it then takes no step at all (no
+                                weight decay, no moments) and stays out of the norm;
+                                its EMA copies are still advanced, as update_ema
+                                (utils/trainer.py:360-370) walks every parameter. */
 } dpk_config;
 
 /* ---- library ---------------------------------------------------------- */
