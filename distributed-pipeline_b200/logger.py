@@ -31,6 +31,14 @@ class Logger:
         self.name2val[key] = old * cnt / (cnt + 1) + val / (cnt + 1)
         self.name2cnt[key] = cnt + 1
 
+    def logkv_mean_n(self, key, mean, n):
+        """``n`` calls of logkv_mean with samples whose mean is ``mean``, in one update."""
+        if n <= 0:
+            return
+        old, cnt = self.name2val[key], self.name2cnt[key]
+        self.name2val[key] = old * cnt / (cnt + n) + mean * n / (cnt + n)
+        self.name2cnt[key] = cnt + n
+
     def dumpkvs(self):
         out = dict(self.name2val)
         if int(os.environ.get("LOCAL_RANK", "0")) == 0:
@@ -78,6 +86,10 @@ def logkv(key, val):
 
 def logkv_mean(key, val):
     get_current().logkv_mean(key, val)
+
+
+def logkv_mean_n(key, mean, n):
+    get_current().logkv_mean_n(key, mean, n)
 
 
 def dumpkvs():

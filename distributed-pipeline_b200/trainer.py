@@ -89,6 +89,9 @@ class TrainLoop:
             fp16_scale_growth=1e-3,
             logger=None,                  # module/object with logkv, logkv_mean, dumpkvs, log, get_current
             grad_allreduce="auto",        # "nvls": the library's symmetric-memory kernels; "nccl"; "auto": nvls if possible
+            schedule_sampler=None,        # upstream's timestep sampler: None | "uniform" | "lossaware" | a ScheduleSampler
+            diffusion_steps=None,         # number of timesteps, needed when the sampler is given by name
+            timestep_key="t",             # micro_batch entry the sampled timesteps are placed under
     ):
         self.logger = logger if logger is not None else _default_logger
         self.model = model
@@ -174,6 +177,13 @@ class TrainLoop:
             self._reducer = None
             self._pair_fused = False
             self.ddp_model = self.model
+
+        # Upstream DiffuSeq's schedule sampler (train_util.py; stripped from the reference at
+        # utils/trainer.py:230-235): timesteps are drawn per microbatch, the loss-aware
+        # kind is fed every rank's (t, loss) records, and losses are weighted by 1/(T p(t)).
+        self.timestep_key = timestep_key
+        self.schedule_sampler = self._make_sampler(schedule_sampler, diffusion_steps)
+        self._loss_log = _DeferredLossLog(self.logger)
 
         self._in_optimize = False
         self._norm_requested = False
@@ -266,6 +276,28 @@ class TrainLoop:
         if torch.is_grad_enabled():
             self._grads_are_zero = False
 
+    def _make_sampler(self, spec, diffusion_steps):
+        if spec is None:
+            return None
+        if isinstance(spec, str):
+            from .sampler import create_named_schedule_sampler
+            if diffusion_steps is None:
+                raise ValueError("schedule_sampler given by name needs diffusion_steps (the number of timesteps)")
+            kw = {}
+            if spec == "lossaware":
+                kw = dict(device=dist_util.dev(), engine=self.opt.engine if self.use_ddp else None,
+                          max_local_batch=max(int(self.microbatch), 1))
+            return create_named_schedule_sampler(spec, diffusion_steps, **kw)
+        return spec
+
+    def log_loss_dict_deferred(self, losses, ts=None, num_timesteps=None, prefix=""):
+        """What upstream's ``log_loss_dict`` logs -- the mean of every entry and, given the timesteps, the
+        per-quartile means -- without its ``.item()`` per value: the few sums are reduced on the device,
+        copied to pinned memory asynchronously and handed to ``logger.logkv_mean`` when the logs are
+        flushed (``log_interval``), so a subclass can call this from its ``log_loss_dict`` hook and keep
+        the step free of host syncs.  The logged numbers are the same running means."""
+        self._loss_log.add(losses, ts, num_timesteps, prefix)
+
     def _zero_grad(self):
         # reference :203-207 zeroes 209 tensors one by one; one fill here, and
         # none at all when the fused pass already left the buffer zeroed.
@@ -278,11 +310,23 @@ class TrainLoop:
             k: v[start_index: start_index + self.microbatch].to(dist_util.dev(), non_blocking=True)
             for k, v in total_batch.items()
         }
+        weights = None
+        if self.schedule_sampler is not None:
+            t, weights = self.schedule_sampler.sample(self.get_batch_length(micro_batch), dist_util.dev())
+            micro_batch[self.timestep_key] = t
         last_batch = (start_index + self.microbatch) >= self.get_batch_length(total_batch)
         if last_batch or not self.use_ddp:
-            return self.compute_losses(micro_batch)
-        with self.ddp_model.no_sync():
-            return self.compute_losses(micro_batch)
+            losses = self.compute_losses(micro_batch)
+        else:
+            with self.ddp_model.no_sync():
+                losses = self.compute_losses(micro_batch)
+        if weights is not None:
+            from .sampler import LossAwareSampler
+            if torch.is_grad_enabled() and isinstance(self.schedule_sampler, LossAwareSampler):
+                # one packed all-gather + one kernel, no host sync (upstream: 3 all_gathers + 2*W*B .item())
+                self.schedule_sampler.update_with_local_losses(micro_batch[self.timestep_key], losses["loss"].detach())
+            losses = {k: v * weights for k, v in losses.items()}   # upstream: (losses["loss"] * weights).mean()
+        return losses
 
     def _microbatch_losses(self, batch):
         """_zero_grad, then the losses of every microbatch in turn, each logged the way the
@@ -423,8 +467,9 @@ class TrainLoop:
             done += 1
 
     def flush_logs(self):
-        """Resolve every pending grad-norm read-back into the logger."""
+        """Resolve every pending read-back (grad norms, deferred loss statistics) into the logger."""
         self._drain_norms(block=True)
+        self._loss_log.drain(block=True)
 
     def log_step(self):
         self.logger.logkv("step", self.step + self.resume_step)
@@ -506,6 +551,76 @@ class TrainLoop:
             return None
         path = os.path.join(os.path.dirname(main_checkpoint), f"opt_{step:06d}.pt")
         return path if os.path.exists(path) else None
+
+
+class _DeferredLossLog:
+    """Pinned ring of per-microbatch loss statistics (f-3: the logging hand-off).  Each ``add`` leaves
+    2 + 8 numbers per key on the device (sum, count, 4 quartile sums, 4 quartile counts), starts an
+    asynchronous copy and returns; ``drain`` feeds finished copies to ``logkv_mean`` with the same
+    running-mean arithmetic as one call per sample (basic_utils/logger.py:350-356)."""
+
+    SLOTS = 64
+
+    def __init__(self, logger):
+        self.logger = logger
+        self._free = []
+        self._inflight = []
+
+    def add(self, losses, ts, num_timesteps, prefix):
+        keys = list(losses.keys())
+        if not keys:
+            return
+        rows = []
+        for k in keys:
+            v = losses[k].detach().reshape(-1).double()
+            row = torch.zeros(10, dtype=torch.float64, device=v.device)
+            row[0] = v.sum()
+            row[1] = v.numel()
+            if ts is not None and num_timesteps:
+                q = (4 * ts.reshape(-1).to(v.device) // int(num_timesteps)).clamp_(0, 3).long()
+                row[2:6].index_add_(0, q, v)
+                row[6:10].index_add_(0, q, torch.ones_like(v))
+            rows.append(row)
+        dev_block = torch.stack(rows)
+        if len(self._inflight) >= self.SLOTS:
+            self.drain(block=False, at_least=1)
+        host = None
+        for i, h in enumerate(self._free):
+            if h.shape == dev_block.shape:
+                host = self._free.pop(i)
+                break
+        if host is None:
+            host = torch.empty(dev_block.shape, dtype=torch.float64, pin_memory=True)
+        host.copy_(dev_block, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._inflight.append((ev, host, [prefix + k for k in keys]))
+
+    def _mean_n(self, key, mean, n):
+        weighted = getattr(self.logger, "logkv_mean_n", None)
+        if weighted is not None:
+            weighted(key, mean, n)
+        else:                      # a logger without the weighted form: n equal samples give the same mean
+            for _ in range(n):
+                self.logger.logkv_mean(key, mean)
+
+    def drain(self, block, at_least=0):
+        done = 0
+        while self._inflight:
+            ev, host, keys = self._inflight[0]
+            if not ev.query():
+                if not block and done >= at_least:
+                    break
+                ev.synchronize()
+            for key, row in zip(keys, host.tolist()):
+                if row[1] > 0:
+                    self.logger.logkv_mean(key, row[0] / row[1])      # upstream: values.mean().item()
+                for q in range(4):
+                    if row[6 + q] > 0:                                 # upstream: one logkv_mean per sample
+                        self._mean_n(f"{key}_q{q}", row[2 + q] / row[6 + q], int(row[6 + q]))
+            self._inflight.pop(0)
+            self._free.append(host)
+            done += 1
 
 
 def update_ema(target_params, source_params, rate=0.99):

@@ -167,7 +167,12 @@ double oracle_adamw_ema_step(int flavour, int dtype, int64_t n, void* p, void* g
 
     /* update_ema: trg.mul_(rate).add_(src, alpha=1-rate) -- add_ fuses alpha*src+trg */
     for (int k = 0; k < n_ema; ++k) {
-      const float rate = (float)ema_rates[k], alpha = (float)(1.0 - ema_rates[k]);
+      const float rate = (float)ema_rates[k];
+      float alpha = (float)(1.0 - ema_rates[k]);
+      /* torch's CPU add kernel narrows `alpha` to the tensor dtype before use (bf16: 1-0.9999 becomes
+       * 1.00136e-4); its CUDA kernel keeps it in fp32.  Pinned by the bf16 golden fixture recorded from
+       * the reference TrainLoop (tests/golden/ref_bf16_clip_ema2_ws1.npz). */
+      if (flavour == ORACLE_CPU) alpha = rnd(dtype, alpha);
       float e = rnd(dtype, load(dtype, ema[k], i) * rate);
       e = rnd(dtype, fmaf(alpha, pi, e));
       store(dtype, ema[k], i, e);

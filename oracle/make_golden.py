@@ -91,11 +91,17 @@ def run(cfg, out_path):
     logger.configure(dir=tmp, format_strs=[])
 
     model = build_model(torch, seed=102)  # same seed on every rank (sidesteps F4)
+    if cfg.get("dtype") == "bf16":
+        # "DiffuSeq-base bf16" of BASELINE configs[2]: the reference keeps no fp32 master copy
+        # (utils/trainer.py:91-92), so AdamW's moments (zeros_like) and the EMA deep copies (:111-113)
+        # are bf16 too and every torch op rounds to bf16
+        model = model.to(torch.bfloat16)
     rec = {"grads": [], "total_norm": [], "logged": [], "lr": [], "p": [], "m": [], "v": [],
            "ema0": [], "ema1": []}
 
     def flat(ts):
-        return np.concatenate([t.detach().reshape(-1).numpy().astype(np.float32) for t in ts])
+        # bf16 values are stored widened to float32 (exact); the fixture's `dtype` field says what they are
+        return np.concatenate([t.detach().reshape(-1).float().numpy().astype(np.float32) for t in ts])
 
     real_clip = torch.nn.utils.clip_grad_norm_
 
@@ -160,7 +166,7 @@ def run(cfg, out_path):
             m=np.stack(rec["m"]), v=np.stack(rec["v"]), ema0=np.stack(rec["ema0"]), ema1=np.stack(rec["ema1"]),
             ema_rates=np.array([float(x) for x in cfg["ema_rate"].split(",")]),
             wd=cfg["wd"], clip=cfg["clip"], lr0=cfg["lr"], learning_steps=cfg["learning_steps"],
-            world_size=int(os.environ.get("WORLD_SIZE", "1")),
+            world_size=int(os.environ.get("WORLD_SIZE", "1")), dtype=cfg.get("dtype", "f32"),
             torch_version=str(torch.__version__))
         print("wrote", out_path)
 
@@ -175,12 +181,16 @@ CONFIGS = {
     # the reference's CPU/gloo DDP path, two ranks, microbatching with no_sync
     "ref_clip_wd_ws2": dict(batch=8, microbatch=4, lr=1e-3, ema_rate="0.9999,0.999", wd=0.01,
                             learning_steps=50, clip=1.0, steps=6, target_scale=30.0, world=2),
+    # every state tensor bf16 (F2/F7): bf16 per-tensor norms, bf16 clip coefficient, bf16 moments and EMA
+    "ref_bf16_clip_ema2_ws1": dict(batch=8, microbatch=4, lr=1e-3, ema_rate="0.9999,0.999", wd=0.01,
+                                   learning_steps=50, clip=1.0, steps=6, target_scale=30.0, world=1, dtype="bf16"),
 }
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--worker", default=None)
+    ap.add_argument("--only", default=None, help="generate just this fixture")
     args = ap.parse_args()
     if args.worker:
         run(CONFIGS[args.worker], os.path.join(OUT, args.worker + ".npz"))
@@ -189,6 +199,8 @@ def main():
         sys.exit("needs /root/reference (build container only)")
     os.makedirs(OUT, exist_ok=True)
     for name, cfg in CONFIGS.items():
+        if args.only and name != args.only:
+            continue
         env = dict(os.environ, WANDB_MODE="disabled")
         if cfg["world"] == 1:
             env.pop("WORLD_SIZE", None)

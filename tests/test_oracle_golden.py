@@ -12,11 +12,13 @@ import torch
 import oracle
 from oracle.torch_port import ReferenceUpdatePort
 
-GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "ref_*.npz")))
+ALL_GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "ref_*.npz")))
+GOLDEN = [p for p in ALL_GOLDEN if "bf16" not in os.path.basename(p)]       # fp32 state
+GOLDEN_BF16 = [p for p in ALL_GOLDEN if "bf16" in os.path.basename(p)]      # every state tensor bf16 (F2/F7)
 
 
 def test_fixtures_present():
-    assert len(GOLDEN) == 3
+    assert len(GOLDEN) == 3 and len(GOLDEN_BF16) == 1
 
 
 def _close(a, b, rtol=1e-6):
@@ -81,6 +83,50 @@ def test_torch_port_reproduces_reference(path):
         assert np.array_equal(flat(port.ema_params[1]).view(np.uint32), z["ema1"][s].view(np.uint32))
         assert abs(port.last_logged_norm - z["logged"][s]) <= 1e-7 * z["logged"][s]
         assert port.opt.param_groups[0]["lr"] == pytest.approx(float(z["lr"][s]), rel=0, abs=0)
+
+
+def _bf16_ulp_distance(a_bits, b_bits):
+    def ordered(b):
+        i = b.astype(np.int64)
+        return np.where(i >= 0x8000, -(i & 0x7fff), i)
+    return np.abs(ordered(a_bits) - ordered(b_bits))
+
+
+@pytest.mark.parametrize("path", GOLDEN_BF16, ids=[os.path.basename(p)[:-4] for p in GOLDEN_BF16])
+def test_c_oracle_bf16_reproduces_reference_trainloop(path):
+    """The reference TrainLoop run with a bf16 model (no fp32 master copy, utils/trainer.py:91-92,111-113):
+    bf16 per-tensor norms, bf16 total norm and clip coefficient (:252-255 -> clip_grad_norm_), bf16 moments,
+    bf16 EMA.  The C oracle's BF16 flavour replayed on the recorded gradients must land on the reference's
+    total norm, both moments, the parameters and both EMA copies bit for bit at every step (an fp32 ulp of
+    MKL's square root does not survive the rounding to bf16 anywhere in this fixture)."""
+    z = np.load(path)
+    assert str(z["dtype"]) == "bf16"
+    numels = z["numels"]
+    off = np.concatenate([[0], np.cumsum(numels)[:-1]])
+    bits = oracle.f32_to_bf16_bits
+    assert np.array_equal(oracle.bf16_bits_to_f32(bits(z["init"])), z["init"])   # fixture values are bf16 values
+    p = bits(z["init"])
+    m, v = np.zeros_like(p), np.zeros_like(p)
+    e = [p.copy(), p.copy()]
+    rates, wd, clip = z["ema_rates"], float(z["wd"]), float(z["clip"])
+    worst = 0
+    for s in range(len(z["lr"])):
+        g = bits(z["grads"][s])
+        r = oracle.grad_norm(oracle.BF16, g, off, numels, 1.0, clip)
+        assert r["total"] == z["total_norm"][s], (s, r["total"], z["total_norm"][s])   # a bf16 value, exactly
+        seg_ss = oracle.adamw_ema_step(oracle.BF16, p, g, m, v, e, rates, float(z["lr"][s]), wd, s + 1, coef=r["coef"],
+                                       grad_mode=1, flavour=oracle.CPU)
+        assert np.array_equal(m, bits(z["m"][s])), f"exp_avg differs at step {s}"
+        assert np.array_equal(v, bits(z["v"][s])), f"exp_avg_sq differs at step {s}"
+        for got, want in ((p, z["p"][s]), (e[0], z["ema0"][s]), (e[1], z["ema1"][s])):
+            d = _bf16_ulp_distance(got, bits(want))
+            worst = max(worst, int(d.max()))
+            assert d.max() == 0
+        # carry the reference's values forward so a one-ulp difference does not compound
+        p[:] = bits(z["p"][s])
+        e[0][:] = bits(z["ema0"][s])
+        e[1][:] = bits(z["ema1"][s])
+    assert worst == 0
 
 
 def test_c_oracle_flavours_agree_to_rounding_and_bf16_roundtrip():
