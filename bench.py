@@ -74,6 +74,8 @@ def parse_args(argv=None):
                     help="N>1: finish the whole all-reduce before the update instead of consuming buckets as they land")
     ap.add_argument("--no-fused-reduce", action="store_true",
                     help="N>1, no clipping: bucketed all-reduce + bucket-overlapped update instead of the one-kernel form")
+    ap.add_argument("--sharded", action="store_true",
+                    help="N>1, no clipping: the opt-in ZeRO-1 style update (each rank updates 1/W, parameters multicast)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="N>1: skip the checked step (the line then has no parity_check)")
@@ -145,6 +147,36 @@ class ClockSampler:
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
                 "samples": len(s)}
+
+
+def bind_to_gpu_numa_node(index):
+    """Pin this process to the CPUs of the NUMA node the GPU hangs off, so that the pinned staging
+    buffers allocated afterwards are first-touched on that node and every rank's uploads travel its
+    own socket's memory controller and PCIe root instead of all sharing one (what a launcher does
+    with numactl).  Best effort: returns a description, or None where the topology is not exposed."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(":", 1)
+        path = f"/sys/bus/pci/devices/{dom[-4:].lower()}:{rest.lower()}/numa_node"
+        with open(path) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"gpu": index, "numa_node": node, "cpus": len(cpus)}
+    except Exception:
+        return None
 
 
 # ------------------------------------------------------------------ reference arm --
@@ -432,6 +464,30 @@ def parity_check(world, rank, dev, use_nvls, verbose=False):
                 for trg, src in zip(lst, ref_p):
                     trg.mul_(rate).add_(src.detach(), alpha=1 - rate)
             up["logged_norm_rel_err"] = max(up["logged_norm_rel_err"], abs(rb[_lib.R_LOGGED_NORM] - sq ** 0.5) / max(sq ** 0.5, 1e-30))
+        # one more step WITH clipping: all-reduce + norm pass as one kernel (dpk_reduce_norm), then the update,
+        # against all-reduce, norm pass, update as separate launches -- same bits expected
+        g = (torch.randn(n, device=dev, generator=gen) * 0.05).to(dtype)
+        clip_state = []
+        for o in (fused, staged):
+            o.flat.grads.copy_(g)
+            keep = [t.clone() for t in (o.flat.params, o.flat.exp_avg, o.flat.exp_avg_sq, *o.flat.emas)]
+            if o is fused:
+                o.reduce_and_step(0.05)
+            else:
+                o.engine.all_buckets_ready()
+                o.engine.wait_allreduce()
+                o.clip_grad_norm(0.05)
+                o.step()
+            torch.cuda.synchronize()
+            res = o.engine.read_results_sync()
+            clip_state.append(([t.clone() for t in (o.flat.params, o.flat.exp_avg, o.flat.exp_avg_sq, *o.flat.emas)],
+                               res[_lib.R_TOTAL_NORM], res[_lib.R_CLIP_COEF], res[_lib.R_LOGGED_NORM]))
+            for t, k in zip((o.flat.params, o.flat.exp_avg, o.flat.exp_avg_sq, *o.flat.emas), keep):
+                t.copy_(k)          # undo: the comparison with torch below is on the three unclipped steps
+            o.step_count -= 1
+        up["clip_step_fused_equals_staged"] = bool(
+            all(torch.equal(a, b) for a, b in zip(clip_state[0][0], clip_state[1][0]))
+            and clip_state[0][1:] == clip_state[1][1:] and clip_state[0][2] < 1.0)
         pairs = list(zip(staged.flat.param_list, ref_p))
         for k in range(len(rates)):
             pairs += list(zip(staged.flat.ema_views[k], ref_ema[k]))
@@ -460,6 +516,7 @@ def parity_check(world, rank, dev, use_nvls, verbose=False):
             up_ok = up["fused_equals_staged"] and up["max_rel_err_vs_torch_adamw"] <= 1e-6 and up["logged_norm_rel_err"] <= 1e-5
         else:
             up_ok = up["fused_equals_staged"] and up["max_ulp_vs_torch_adamw"] <= 1 and up["logged_norm_rel_err"] <= 2 ** -7
+        up_ok = up_ok and up["clip_step_fused_equals_staged"]
         ar["ok"], up["ok"] = bool(ar_ok), bool(up_ok)
         ok = ok and ar_ok and up_ok
         worst_ulp = max(worst_ulp, up["max_ulp_vs_torch_adamw"])
@@ -509,7 +566,8 @@ def run_ours(args):
     params = [torch.nn.Parameter((torch.randn(s, generator=gen, device=dev) * 0.02).to(tdt)) for s in shapes]
     opt = FusedAdamW(params, lr=LR, weight_decay=wd, ema_rates=rates, grad_mode=gm, tile_elems=args.tile_elems,
                      bucket_cap_mb=args.bucket_mb if world > 1 else 128,
-                     symmetric_grads=world > 1 and args.allreduce == "nvls")
+                     symmetric_grads=world > 1 and args.allreduce == "nvls",
+                     sharded=bool(args.sharded and world > 1 and args.allreduce == "nvls"))
     opt.fused_reduce = not args.no_fused_reduce
     del params
     eng, flat = opt.engine, opt.flat
@@ -534,6 +592,11 @@ def run_ours(args):
                     print(f"[bench] symmetric-memory all-reduce unavailable ({why}); using NCCL", file=sys.stderr)
                 eng.nvls = False
                 args.allreduce = "nccl"
+    if opt.sharded:
+        args.no_e2e = True     # the host-gradient entry point (step_from_host) is a replica-path API
+        if not eng.nvls:
+            sys.exit("--sharded needs the symmetric-memory path")
+        eng.enable_shard(flat.params)
     parity = None
     if world > 1 and not args.no_parity:
         parity = parity_check(world, rank, dev, eng.nvls)
@@ -542,8 +605,11 @@ def run_ours(args):
     grads_src = (torch.randn(flat.layout.n_elems, generator=ggen, device=dev) * sigma).to(tdt)
     flat.grads.copy_(grads_src)
     n_buckets = len(eng.buckets)
-    one_kernel = bool(world > 1 and eng.nvls and opt.fused_reduce and not args.no_overlap and clip <= 0
+    one_kernel = bool(world > 1 and eng.nvls and (opt.fused_reduce or opt.sharded) and not args.no_overlap and clip <= 0
                       and args.grad_mode == "keep")
+    switch = world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1"
+    # with clipping: all-reduce + norm pass as one kernel (dpk_reduce_norm) where the switch reduces
+    norm_kernel = bool(world > 1 and eng.nvls and opt.fused_reduce and not args.no_overlap and clip > 0 and switch)
 
     def device_step():
         if world > 1 and not args.no_overlap:
@@ -615,6 +681,8 @@ def run_ours(args):
     if one_kernel:
         pair = world == 2 and os.environ.get("DPK_FORCE_MULTIMEM") != "1"
         kname = "fused_update_kernel<kGradPair> (all-reduce inside)" if pair else "reduce_update_kernel (all-reduce inside)"
+        if opt.sharded:
+            kname = "shard_update_kernel (reduce-scatter + 1/W update + all-gather)"
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_avg": k_ms, "kernel_ms_min": min(kernel_ms) if kernel_ms else None,
@@ -622,11 +690,12 @@ def run_ours(args):
                 "frac_of_nominal_8TBps": achieved / 8000.0}
     if norm_ms:
         s = 4 if dtype == "f32" else 2
-        per_norm = n_buckets if (world > 1 and not args.no_overlap and clip > 0) else 1
+        per_norm = n_buckets if (world > 1 and not args.no_overlap and clip > 0 and not norm_kernel) else 1
         if per_norm > 1:
             norm_ms = [sum(norm_ms[i:i + per_norm]) for i in range(0, len(norm_ms) - per_norm + 1, per_norm)]
         n_ms = sum(norm_ms) / len(norm_ms)
-        roofline["norm_pass"] = {"kernel": "sumsq_tiles_kernel", "kernel_ms_avg": n_ms,
+        roofline["norm_pass"] = {"kernel": "reduce_norm_kernel (all-reduce inside)" if norm_kernel else "sumsq_tiles_kernel",
+                                 "kernel_ms_avg": n_ms,
                                  "achieved": n_params * s / (n_ms * 1e-3) / 1e9,
                                  "frac": n_params * s / (n_ms * 1e-3) / 1e9 / peak}
 
@@ -636,6 +705,8 @@ def run_ours(args):
         S = flat.layout.n_elems * (4 if dtype == "f32" else 2)          # message bytes per rank
         if one_kernel:
             c_ms, c_kernel, c_n = k_ms, kname, len(kernel_ms)
+        elif norm_kernel:
+            c_ms, c_kernel, c_n = roofline["norm_pass"]["kernel_ms_avg"], "reduce_norm_kernel (all-reduce inside)", len(norm_ms)
         else:
             per = [sum(comm_ms[i:i + n_buckets]) for i in range(0, len(comm_ms) - n_buckets + 1, n_buckets)]
             c_ms = sum(per) / len(per) if per else float("nan")
@@ -658,12 +729,14 @@ def run_ours(args):
                          "wire_bytes_per_direction": wire,
                          "wire_frac": wire / (c_ms * 1e-3) / 1e9 / NVLINK_NOMINAL_GBS,
                          "wire_frac_of_measured_770": wire / (c_ms * 1e-3) / 1e9 / NVLINK_MEASURED_GBS,
-                         "note": ("timed with CUDA events around the kernel, beside the update it overlaps"
-                                  if not one_kernel else "the collective and the update are the same kernel")}
+                         "note": ("the collective and the update are the same kernel" if one_kernel else
+                                  "the collective and the norm pass are the same kernel" if norm_kernel else
+                                  "timed with CUDA events around the kernel, beside the pass it overlaps")}
 
     # ---- end to end: gradients from pinned host memory, result block read back -----
     e2e = None
     if not args.no_e2e:
+        numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None
         host_g = torch.empty(flat.layout.n_elems, dtype=tdt, pin_memory=True)
         host_g.copy_(grads_src)
         host_res = torch.empty(_lib.R_COUNT, dtype=torch.float64, pin_memory=True)
@@ -695,8 +768,10 @@ def run_ours(args):
         e2e = {"value": world * n_params * bpp / (e_ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": e_ms,
                "steps": e_steps, "h2d_bytes_per_step": host_g.numel() * host_g.element_size(),
                "d2h_bytes_per_step": host_res.numel() * host_res.element_size(), "last_grad_norm": norm,
+               "staging_numa": numa,
                "api": "FusedAdamW.step_from_host (TrainLoop.opt): pinned host gradients, bucket-pipelined upload"}
 
+    opt_sharded = opt.sharded
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         del opt, eng, flat
@@ -719,7 +794,8 @@ def run_ours(args):
                        "allreduce": (("own kernels over symmetric memory (NVSwitch multimem for W>=4, pair exchange for W=2)"
                                       if args.allreduce == "nvls" else "ncclAllReduce(avg)") if world > 1 else None),
                        "update_overlaps_allreduce": bool(world > 1 and not args.no_overlap),
-                       "one_kernel_allreduce_update": one_kernel,
+                       "one_kernel_allreduce_update": one_kernel, "one_kernel_allreduce_norm": norm_kernel,
+                       "sharded_update": bool(opt_sharded),
                        "grad_sigma": sigma},
             "roofline": roofline, "roofline_comm": roofline_comm, "parity_check": parity,
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,

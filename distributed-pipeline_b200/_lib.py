@@ -86,6 +86,10 @@ SIGNATURES = {
     "dpk_fused_update_finish": (C.c_int, [_VP, C.c_int32, _VP]),
     "dpk_reduce_update_pair": (C.c_int, [_VP, C.c_double, C.c_double, C.c_int64, C.c_double, _VP]),
     "dpk_reduce_update": (C.c_int, [_VP, C.c_double, C.c_double, C.c_int64, C.c_double, _VP]),
+    "dpk_reduce_norm": (C.c_int, [_VP, C.c_double, C.c_double, _VP]),
+    "dpk_bind_shard": (C.c_int, [_VP, _VP]),
+    "dpk_shard_update": (C.c_int, [_VP, C.c_double, C.c_double, C.c_int64, C.c_double, _VP]),
+    "dpk_shard_gather": (C.c_int, [_VP, _VP]),
     "dpk_set_option": (C.c_int, [_VP, C.c_int32, C.c_int64]),
     "dpk_result_ptr": (C.c_int, [_VP, C.POINTER(_VP)]),
     "dpk_read_result_sync": (C.c_int, [_VP, C.POINTER(C.c_double), _VP]),

@@ -155,7 +155,7 @@ static int launch_update_impl(dpk_handle* h, const StepScalars& sc, int use_coef
   a.p = (T*)h->p; a.g = (T*)h->g; a.m = (T*)h->m; a.v = (T*)h->v;
   for (int k = 0; k < K; ++k) a.ema[k] = (T*)h->ema[k];
   a.peer_g = (GM == kGradPair) ? (const T*)h->peer_grads[1 - h->rank] : nullptr;
-  a.unit_flags = nullptr; a.flag_target = 0; a.unit_shift = 0; a.timeout_ns = 0; a.results_rw = h->d_results;
+  memset(&a.fw, 0, sizeof(a.fw));
   a.tiles = h->d_tiles;
   a.tile_begin = tile_begin;
   a.tile_end = tile_end;
@@ -791,6 +791,106 @@ int dpk_reduce_update(dpk_handle* h, double lr, double weight_decay, int64_t ada
   const StepScalars sc = step_scalars(h, lr, weight_decay, adam_step, inv_scale);
   if (int rc = launch_reduce_update(h, sc, st)) return rc;
   return dpk_fused_update_finish(h, 0, stream);
+}
+
+// Four or more ranks, with clipping: the all-reduce and pass 1 as one kernel (see
+// dpk_nvls.cu: reduce_norm_kernel); dpk_fused_update(use_clip_coef=1) follows.
+int dpk_reduce_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream) {
+  if (!h) { set_error("dpk_reduce_norm: null handle"); return DPK_E_BADARG; }
+  if (!h->bound || !h->mc_grads || h->world < 2) {
+    set_error("dpk_reduce_norm: needs two or more ranks and dpk_bind_nvls");
+    return DPK_E_STATE;
+  }
+  if (h->world == 2 && !h->force_multimem) {
+    // two ranks have no switch-reduced form: pair all-reduce of every bucket, norm bucket by bucket behind it
+    if (int rc = dpk_all_buckets_ready(h, stream)) return rc;
+    for (int b = 0; b < (int)h->buckets.size(); ++b) {
+      if (int rc = dpk_wait_bucket(h, b, stream)) return rc;
+      if (int rc = dpk_grad_norm_bucket(h, b, inv_scale, stream)) return rc;
+    }
+    return dpk_grad_norm_finish(h, max_norm, stream);
+  }
+  {
+    std::lock_guard<std::mutex> lock(h->mu);
+    DPK_GUARD(h);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (int rc = pair_sync(h, st)) return rc;  // every rank's gradients are complete
+    if (int rc = launch_reduce_norm(h, (float)inv_scale, st)) return rc;
+  }
+  return dpk_grad_norm_finish(h, max_norm, stream);
+}
+
+// ---- sharded (ZeRO-1 style) update, opt-in ------------------------------------
+
+int dpk_bind_shard(dpk_handle* h, void* mc_params) {
+  if (!h || !mc_params || ((uintptr_t)mc_params & 15u)) { set_error("dpk_bind_shard: bad argument"); return DPK_E_BADARG; }
+  if (!h->bound || !h->mc_grads || h->world < 2) {
+    set_error("dpk_bind_shard: bind buffers, the communicator and dpk_bind_nvls first");
+    return DPK_E_STATE;
+  }
+  std::lock_guard<std::mutex> lock(h->mu);
+  h->mc_params = mc_params;
+  return 0;
+}
+
+int dpk_shard_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step, double inv_scale,
+                     void* stream) {
+  if (!h) { set_error("dpk_shard_update: null handle"); return DPK_E_BADARG; }
+  if (!h->bound || !h->mc_grads || !h->mc_params || h->world < 2 || !h->comm) {
+    set_error("dpk_shard_update: needs two or more ranks, dpk_bind_nvls and dpk_bind_shard");
+    return DPK_E_STATE;
+  }
+  if (adam_step < 1) { set_error("dpk_shard_update: adam_step %lld < 1", (long long)adam_step); return DPK_E_BADARG; }
+  const NcclApi* api = nccl_api();
+  if (!api) return DPK_E_NCCL;
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = pair_sync(h, st)) return rc;  // every rank's gradients are complete
+  const StepScalars sc = step_scalars(h, lr, weight_decay, adam_step, inv_scale);
+  if (int rc = launch_shard_update(h, sc, st)) return rc;
+  if (int rc = pair_sync(h, st)) return rc;  // every replica holds every rank's new parameters; gradients are free again
+  h->shards_dirty = true;
+  // the logged norm: per-tensor sums over this rank's chunks, summed over the ranks, then finalised
+  if (h->n_seg > 0) {
+    const int grid = std::min(h->n_seg, 4 * h->sm_count);
+    segment_reduce_kernel<<<grid, kThreads, 0, st>>>(h->d_partials_post, h->d_seg_tile_begin, h->d_seg_sumsq,
+                                                     h->d_seg_bad, h->n_seg, h->chunks_per_tile);
+    h->launches++;
+    DPK_CUDA(cudaGetLastError());
+    DPK_NCCL(api->AllReduce(h->d_seg_sumsq, h->d_seg_sumsq, (size_t)h->n_seg, ncclFloat64, ncclSum, h->comm, st));
+  }
+  if (h->dtype == DPK_F32)
+    finalize_logged_kernel<float><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, 0, h->d_results);
+  else
+    finalize_logged_kernel<__nv_bfloat16><<<1, kThreads, 0, st>>>(h->d_seg_sumsq, h->n_seg, 0, h->d_results);
+  h->launches++;
+  DPK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int dpk_shard_gather(dpk_handle* h, void* stream) {
+  if (!h) { set_error("dpk_shard_gather: null handle"); return DPK_E_BADARG; }
+  if (!h->bound) { set_error("dpk_shard_gather: buffers not bound"); return DPK_E_STATE; }
+  if (!h->shards_dirty || h->world < 2) return 0;
+  const NcclApi* api = nccl_api();
+  if (!api || !h->comm) { set_error("dpk_shard_gather: communicator not initialised"); return DPK_E_STATE; }
+  std::lock_guard<std::mutex> lock(h->mu);
+  DPK_GUARD(h);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int rc = launch_shard_zero_foreign(h, st)) return rc;
+  const size_t words = (size_t)h->n_elems * elem_size(h->dtype) / 4;   // n_elems is a whole number of 16-byte vectors
+  void* bufs[2 + DPK_MAX_EMA] = {h->m, h->v};
+  for (int k = 0; k < h->n_ema; ++k) bufs[2 + k] = h->ema[k];
+  DPK_NCCL(api->GroupStart());
+  ncclResult_t r = ncclSuccess;
+  for (int i = 0; r == ncclSuccess && i < 2 + h->n_ema; ++i)
+    r = api->AllReduce(bufs[i], bufs[i], words, ncclUint32, ncclSum, h->comm, st);  // x + 0 + ... + 0: every bit survives
+  ncclResult_t r2 = api->GroupEnd();
+  if (r != ncclSuccess) return nccl_fail(r, "ncclAllReduce (shard gather)");
+  if (r2 != ncclSuccess) return nccl_fail(r2, "ncclGroupEnd");
+  h->shards_dirty = false;
+  return 0;
 }
 
 int dpk_fused_update_finish(dpk_handle* h, int32_t skip_if_nonfinite, void* stream) {

@@ -56,6 +56,9 @@ namespace dpk {
 int nvls_allreduce(dpk_handle* h, const Bucket& bk, bool start_barrier, cudaStream_t st);
 int pair_sync(dpk_handle* h, cudaStream_t st);  // barrier between all ranks, a kernel of its own
 int launch_reduce_update(dpk_handle* h, const StepScalars& sc, cudaStream_t st);
+int launch_reduce_norm(dpk_handle* h, float inv_scale, cudaStream_t st);
+int launch_shard_update(dpk_handle* h, const StepScalars& sc, cudaStream_t st);
+int launch_shard_zero_foreign(dpk_handle* h, cudaStream_t st);
 
 struct Bucket {
   int seg_begin, seg_end;     // tensors [seg_begin, seg_end)
@@ -115,6 +118,8 @@ struct dpk_handle {
   // NVLS all-reduce (dpk_nvls.cu): multicast mapping of the gradient buffer and
   // of the per-block signal counters, bound by the caller
   void* mc_grads = nullptr;
+  void* mc_params = nullptr;   // dpk_bind_shard: multicast mapping of the parameter buffer
+  bool shards_dirty = false;   // moments / EMA copies currently valid on the owner rank only
   void* peer_grads[DPK_MAX_RANKS] = {nullptr};  // every rank's mapping of the gradient buffer
   unsigned* mc_signal = nullptr;
   const unsigned* local_signal = nullptr;
@@ -128,7 +133,7 @@ struct dpk_handle {
   int flag_base = 0, flag_slots = 0;
   unsigned flag_epoch = 0;   // value every unit counter has after the steps enqueued so far
   int unit_shift = 0;        // log2(vectors per unit)
-  int fused_comm_blocks = 64, fused_update_blocks = 0;
+  int fused_comm_blocks = 32, fused_update_blocks = 0;
   unsigned long long peer_timeout_ns = 600ull * 1000 * 1000 * 1000;  // DPK_OPT_PEER_TIMEOUT_MS
 
   // instrumentation

@@ -246,6 +246,53 @@ __device__ __forceinline__ double block_sum_f64(double v, double* smem) {
   return r;
 }
 
+// ---- waiting for gradients that other GPUs are still delivering ---------------
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* addr) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ uint4 ld_sys(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+
+// The fused W-rank passes (dpk_nvls.cu) read a gradient vector only after the
+// arrival counter of its unit (2^shift vectors) shows that every owner rank has
+// written this step's average into this rank's buffer.
+struct FlagWait {
+  const unsigned* flags;   // per-unit arrival counters on this rank
+  unsigned target;         // value a counter has once all ranks delivered this step
+  int shift;               // log2(vectors per unit)
+  unsigned long long timeout_ns;
+  double* results;         // result block: DPK_R_COMM_TIMEOUT is raised on give-up
+};
+
+// False if the wait was abandoned (a peer is gone).  The acquire orders the
+// caller's following gradient load behind the owners' stores.
+__device__ __forceinline__ bool flag_wait(const FlagWait& fw, long long vidx) {
+  const unsigned* flag = fw.flags + (vidx >> fw.shift);
+  if ((int)(ld_acquire_sys_u32(flag) - fw.target) >= 0) return true;
+  const unsigned long long t0 = global_timer_ns();
+  unsigned spins = 0;
+  while ((int)(ld_acquire_sys_u32(flag) - fw.target) < 0) {
+    __nanosleep(64);
+    if ((++spins & 0x3ffu) == 0) {
+      const bool late = global_timer_ns() - t0 > fw.timeout_ns;
+      if (late) fw.results[DPK_R_COMM_TIMEOUT] = 1.0;
+      if (late || *reinterpret_cast<const volatile double*>(fw.results + DPK_R_COMM_TIMEOUT) != 0.0) return false;
+    }
+  }
+  return true;
+}
+
 // One tile's sum of squares and non-finite indicator, per thread (the caller
 // reduces across the block).  Shared by the handle path and dpk_grad_norm_static
 // so that both add the same numbers in the same order.  Full vectors carry no
@@ -253,14 +300,28 @@ __device__ __forceinline__ double block_sum_f64(double v, double* smem) {
 // that would own it anyway and is added last.  `tail_by_element`: read the ragged
 // tail element by element (the caller's array may end exactly there) instead of
 // as one masked 16-byte vector (flat buffers are padded).
-template <typename T, int U, bool STAGED = false>
+// SRC: where the vectors come from -- kSrcGlobal: read-only global loads;
+// kSrcStaged: the tile already sits in shared memory (bulk-copied there);
+// kSrcFlagged: global memory that other GPUs are writing during this kernel, each
+// vector loaded (coherently) only once its unit has arrived (fw, vbase = index of
+// the tile's first vector in the flat buffer).
+constexpr int kSrcGlobal = 0, kSrcStaged = 1, kSrcFlagged = 2;
+
+template <typename T, int U, int SRC = kSrcGlobal>
 __device__ __forceinline__ void tile_sumsq(const T* __restrict__ g_tile, int len, float inv_scale,
-                                           bool tail_by_element, float& acc, float& nonfin) {
+                                           bool tail_by_element, float& acc, float& nonfin,
+                                           const FlagWait* fw = nullptr, long long vbase = 0) {
   using Tr = ElemTraits<T>;
   constexpr int VE = Tr::VE;
   const uint4* gv = reinterpret_cast<const uint4*>(g_tile);
-  // STAGED: the tile already sits in shared memory (bulk-copied there), plain loads
-  auto ld = [](const uint4* p) { return STAGED ? *p : ld_readonly(p); };
+  auto ld = [&](const uint4* p) -> uint4 {
+    if (SRC == kSrcStaged) return *p;
+    if (SRC == kSrcFlagged) {
+      flag_wait(*fw, vbase + (p - gv));   // on give-up the flag is raised and the data no longer matter
+      return ld_sys(p);
+    }
+    return ld_readonly(p);
+  };
   const int nfull = len / VE;
   for (int v0 = threadIdx.x; v0 < nfull; v0 += kThreads * U) {
     uint4 raw[U];
@@ -406,26 +467,56 @@ __device__ __forceinline__ void finalize_logged_block(const double* __restrict__
 // finalises -- was built and measured in round 2: the per-tile fence + ticket +
 // extra barrier cost 26 us on DiffuSeq-base (0.057 -> 0.083 ms), more than the
 // launch it saves.  The tail is one small launch instead: norm_tail_kernel.)
+// The tile loop of one worker block out of n_workers.  One barrier per tile: the
+// warp totals and the per-warp non-finite flags travel through the same
+// (double-buffered) exchange.  The order of the additions is block_sum's -- lane
+// tree, then warp 0 over the eight warp totals -- so the partials are
+// bit-identical to the three-barrier form dpk_grad_norm_static uses.
+template <typename T, int U, int SRC>
+__device__ __forceinline__ void sumsq_tiles(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin,
+                                            int tile_end, float inv_scale, TilePartial* __restrict__ partials,
+                                            int worker, int n_workers, const FlagWait* fw) {
+  __shared__ float red[2][kThreads / 32];
+  __shared__ unsigned red_bad[2][kThreads / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int buf = 0;
+  for (int t = tile_begin + worker; t < tile_end; t += n_workers) {
+    const Tile tile = tiles[t];
+    float acc = 0.f, nonfin = 0.f;
+    // a tensor without a gradient is not part of the norm (clip_grad_norm_ skips grad=None)
+    if (!(tile.seg & kTileFrozen))
+      tile_sumsq<T, U, SRC>(g + tile.start, tile.len, inv_scale, false, acc, nonfin, fw,
+                            tile.start / ElemTraits<T>::VE);
+    const unsigned warp_bad = __any_sync(0xffffffffu, nonfin != nonfin) ? 1u : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc = __fadd_rn(acc, __shfl_down_sync(0xffffffffu, acc, o));
+    if (lane == 0) {
+      red[buf][warp] = acc;
+      red_bad[buf][warp] = warp_bad;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      float r = (lane < kThreads / 32) ? red[buf][lane] : 0.f;
+      const unsigned b = (lane < kThreads / 32) ? red_bad[buf][lane] : 0u;
+      const unsigned any_bad = __any_sync(0xffffffffu, b != 0u) ? 1u : 0u;
+#pragma unroll
+      for (int o = 4; o > 0; o >>= 1) r = __fadd_rn(r, __shfl_down_sync(0xffffffffu, r, o));
+      if (lane == 0) {
+        TilePartial p;
+        p.sumsq = r;
+        p.bad = any_bad;
+        partials[t] = p;
+      }
+    }
+    buf ^= 1;
+  }
+}
+
 template <typename T, int U>
 __global__ void __launch_bounds__(kThreads)
 sumsq_tiles_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, int tile_begin,
                    int tile_end, float inv_scale, TilePartial* __restrict__ partials) {
-  __shared__ float red[kThreads / 32];
-  for (int t = tile_begin + blockIdx.x; t < tile_end; t += gridDim.x) {
-    const Tile tile = tiles[t];
-    float acc = 0.f, nonfin = 0.f;
-    // a tensor without a gradient is not part of the norm (clip_grad_norm_ skips grad=None)
-    if (!(tile.seg & kTileFrozen)) tile_sumsq<T, U>(g + tile.start, tile.len, inv_scale, false, acc, nonfin);
-    const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
-    const int any_bad = __syncthreads_or((int)bad);
-    const float s = block_sum(acc, red);
-    if (threadIdx.x == 0) {
-      TilePartial p;
-      p.sumsq = s;
-      p.bad = any_bad ? 1u : 0u;
-      partials[t] = p;
-    }
-  }
+  sumsq_tiles<T, U, kSrcGlobal>(g, tiles, tile_begin, tile_end, inv_scale, partials, blockIdx.x, gridDim.x, nullptr);
 }
 
 // The same pass with the tiles staged through shared memory by the TMA engine:
@@ -486,7 +577,7 @@ sumsq_tiles_tma_kernel(const T* __restrict__ g, const Tile* __restrict__ tiles, 
     }
     const int len = (desc[s].seg & kTileFrozen) ? 0 : desc[s].len;
     float acc = 0.f, nonfin = 0.f;
-    tile_sumsq<T, U, true>(reinterpret_cast<const T*>(stage_mem + (size_t)s * tile_bytes_max), len, inv_scale, false,
+    tile_sumsq<T, U, kSrcStaged>(reinterpret_cast<const T*>(stage_mem + (size_t)s * tile_bytes_max), len, inv_scale, false,
                            acc, nonfin);
     const unsigned bad = (nonfin != nonfin) ? 1u : 0u;
     const int any_bad = __syncthreads_or((int)bad);  // also: every thread is done reading stage s
@@ -560,6 +651,16 @@ norm_tail_kernel(const TilePartial* __restrict__ partials, const int* __restrict
   if (threadIdx.x == 0) *ticket = 0u;
 }
 
+// finalize_logged_block as a launch of its own (the sharded update sums the
+// per-tensor values over the ranks in between).
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+finalize_logged_kernel(const double* __restrict__ seg_sumsq, int n_seg, int skip_if_nonfinite,
+                       double* __restrict__ results) {
+  __shared__ double red[kThreads / 32];
+  finalize_logged_block<T>(seg_sumsq, n_seg, skip_if_nonfinite, results, red);
+}
+
 // The tail of the fused pass as ONE launch: per-tensor sums of the per-chunk
 // partials, then -- in whichever block finishes last -- the logged norm.
 template <typename T>
@@ -598,23 +699,49 @@ constexpr int kGradPair = 3;
 // that own each range WHILE this kernel runs; a vector may be read once the
 // per-unit arrival counter says all owners have delivered their part of it.
 constexpr int kGradFlagged = 4;
+// Internal gradient mode of the sharded update (dpk_shard_update): this rank owns the
+// chunk; its gradient is the switch-reduced sum of all W copies (multimem.ld_reduce)
+// times 1/W, taken straight into registers, and the new parameters are multicast
+// into every rank's replica (multimem.st).  Moments and EMA copies stay local.
+constexpr int kGradSwitch = 5;
 
-__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* addr) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-  return t;
-}
+// ---- NVSwitch multimem accesses: one instruction, W copies ----------------------
+template <typename T> struct Multimem;
+template <> struct Multimem<float> {
+  static __device__ __forceinline__ uint4 ld_reduce(const uint4* mc) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
+    return r;
+  }
+  static __device__ __forceinline__ uint4 scale(uint4 v, float s) {
+    v.x = __float_as_uint(__fmul_rn(__uint_as_float(v.x), s));
+    v.y = __float_as_uint(__fmul_rn(__uint_as_float(v.y), s));
+    v.z = __float_as_uint(__fmul_rn(__uint_as_float(v.z), s));
+    v.w = __float_as_uint(__fmul_rn(__uint_as_float(v.w), s));
+    return v;
+  }
+};
+template <> struct Multimem<__nv_bfloat16> {
+  static __device__ __forceinline__ uint4 ld_reduce(const uint4* mc) {
+    uint4 r;  // W bf16 addends accumulated in fp32 inside the switch, rounded once
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
+    return r;
+  }
+  static __device__ __forceinline__ uint4 scale(uint4 v, float s) {
+    float x[8];
+    ElemTraits<__nv_bfloat16>::unpack(v, x);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] = __fmul_rn(x[j], s);
+    return ElemTraits<__nv_bfloat16>::pack(x);  // rounds to bf16
+  }
+};
 
-__device__ __forceinline__ uint4 ld_sys(const uint4* p) {
-  uint4 r;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
-  return r;
+__device__ __forceinline__ void multimem_st(uint4* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
 }
 
 // (a+b)/2 per element, one rounding to the state dtype: ncclAvg's / DDP's result for two ranks
@@ -637,13 +764,10 @@ struct UpdateArgs {
   T* v;
   T* ema[K > 0 ? K : 1];
   const T* peer_g;           // kGradPair only: the other rank's gradient buffer (peer mapping)
-  // kGradFlagged only: arrival counter of every unit of 2^unit_shift vectors, the
-  // value it has once all ranks delivered this step's average, and how long to wait
-  const unsigned* unit_flags;
-  unsigned flag_target;
-  int unit_shift;
-  unsigned long long timeout_ns;
-  double* results_rw;        // same block as `results`, writable (timeout flag)
+  FlagWait fw;               // kGradFlagged only
+  const uint4* mc_g;         // kGradSwitch only: multicast addresses of the gradient and parameter buffers
+  uint4* mc_p;
+  float inv_world;
   const Tile* tiles;
   int tile_begin, tile_end;  // this launch covers tiles [tile_begin, tile_end)
   int chunk_elems;           // elements per work item: one 16-byte vector per thread
@@ -657,13 +781,9 @@ struct UpdateArgs {
 
 // Returns true only in kGradFlagged mode, when the wait for a peer was abandoned
 // (nothing has been stored for this vector then).
-// `frozen`: the tensor has no gradient (requires_grad=False): torch.optim.AdamW
-// skips it entirely -- no decay, no moments, no step (optim/adam.py:232-238 collects
-// only params with a grad) -- while update_ema (utils/trainer.py:360-370) still
-// walks every parameter.  Its gradient bytes are not read as data.
 template <typename T, int K, int GM, bool FULL>
 __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long long vidx, int rem,
-                                              float coef, float& acc, bool frozen) {
+                                              float coef, float& acc) {
   using Tr = ElemTraits<T>;
   uint4* pv = reinterpret_cast<uint4*>(a.p) + vidx;
   uint4* gv = reinterpret_cast<uint4*>(a.g) + vidx;
@@ -672,7 +792,8 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
 
   // all loads of this vector are issued before any arithmetic
   uint4 rg = make_uint4(0, 0, 0, 0);
-  if (GM != kGradFlagged) rg = (GM == DPK_GRAD_KEEP || GM == kGradPair) ? ld_readonly(gv) : ld_stream(gv);
+  if (GM == kGradSwitch) rg = Multimem<T>::ld_reduce(a.mc_g + vidx);  // reduce-scatter: W copies summed in the switch
+  else if (GM != kGradFlagged) rg = (GM == DPK_GRAD_KEEP || GM == kGradPair) ? ld_readonly(gv) : ld_stream(gv);
   uint4 rpeer = make_uint4(0, 0, 0, 0);
   if (GM == kGradPair) rpeer = ld_sys(reinterpret_cast<const uint4*>(a.peer_g) + vidx);  // over NVLink
   const uint4 rp = ld_stream(pv);
@@ -683,24 +804,13 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
   for (int k = 0; k < K; ++k) re[k] = ld_stream(reinterpret_cast<uint4*>(a.ema[k]) + vidx);
   if (GM == kGradFlagged) {
     // the state loads above are in flight while this thread waits for the owners of
-    // its vector's unit; the acquire orders the gradient load behind their stores
-    const unsigned* flag = a.unit_flags + (vidx >> a.unit_shift);
-    if ((int)(ld_acquire_sys_u32(flag) - a.flag_target) < 0) {
-      const unsigned long long t0 = global_timer_ns();
-      unsigned spins = 0;
-      while ((int)(ld_acquire_sys_u32(flag) - a.flag_target) < 0) {
-        __nanosleep(64);
-        if ((++spins & 0x3ffu) == 0) {
-          const bool late = global_timer_ns() - t0 > a.timeout_ns;
-          if (late) a.results_rw[DPK_R_COMM_TIMEOUT] = 1.0;
-          if (late || *reinterpret_cast<const volatile double*>(a.results + DPK_R_COMM_TIMEOUT) != 0.0) return true;
-        }
-      }
-    }
+    // its vector's unit
+    if (!flag_wait(a.fw, vidx)) return true;
     rg = ld_sys(gv);  // written by other GPUs during this kernel: not through the non-coherent path
   }
 
   if (GM == kGradPair) rg = average2<T>(rg, rpeer);  // the all-reduce, without a pass of its own
+  if (GM == kGradSwitch) rg = Multimem<T>::scale(rg, a.inv_world);
 
   uint4 wg = rg, wp = rp, wm = rm, wv = rv;
   uint4 we[K > 0 ? K : 1];
@@ -715,7 +825,6 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
     Tr::unpack4(rp, c, p);
     Tr::unpack4(rm, c, m);
     Tr::unpack4(rv, c, v);
-    if (!frozen) {
     // Each block below is one torch kernel: compute in fp32, then the store to the
     // state dtype (rnd4*: nothing for fp32, round-to-nearest-even for bf16).
     // grad.mul_(1/2^lg) (upstream loss-scale) and _foreach_mul_(grads, coef): a
@@ -767,7 +876,6 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
 #pragma unroll
     for (int j = 0; j < 4; ++j) p[j] = __fmaf_rn(s.neg_step, __fdiv_rn(m[j], d[j]), p[j]);
     Tr::rnd4_store(p, wp, c);
-    }  // !frozen
 
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -798,14 +906,47 @@ __device__ __forceinline__ bool update_vector(const UpdateArgs<T, K>& a, long lo
   // copy of the index instead of being kept alive across the arithmetic: 2 live
   // registers instead of 2 per stream, which is what the 64-register bf16 build spilled.
   long long sidx = vidx;
-  if (sizeof(T) == 2) asm volatile("" : "+l"(sidx));
-  st_stream(reinterpret_cast<uint4*>(a.p) + sidx, wp);
+  asm volatile("" : "+l"(sidx));
+  if (GM == kGradSwitch) multimem_st(a.mc_p + sidx, wp);   // all-gather: every replica receives the new parameters
+  else st_stream(reinterpret_cast<uint4*>(a.p) + sidx, wp);
   st_stream(reinterpret_cast<uint4*>(a.m) + sidx, wm);
   st_stream(reinterpret_cast<uint4*>(a.v) + sidx, wv);
   if (GM == DPK_GRAD_CLIPPED || GM == DPK_GRAD_ZERO) st_stream(reinterpret_cast<uint4*>(a.g) + sidx, wg);
 #pragma unroll
   for (int k = 0; k < K; ++k) st_stream(reinterpret_cast<uint4*>(a.ema[k]) + sidx, we[k]);
   return false;
+}
+
+// A vector of a tensor that has no gradient (requires_grad=False): torch.optim.AdamW
+// skips such a parameter entirely -- no decay, no moments, no step (optim/adam.py
+// collects only parameters with a grad) -- while update_ema (utils/trainer.py:360-370)
+// still walks every parameter.  So: p, m, v and the gradient bytes are left alone
+// (the latter not even read), only the EMA copies advance.  Kept apart from
+// update_vector so that the hot path carries no trace of it.
+template <typename T, int K>
+__device__ __forceinline__ void frozen_vector(const UpdateArgs<T, K>& a, long long vidx, int rem) {
+  using Tr = ElemTraits<T>;
+  if (K == 0) return;
+  const uint4 rp = ld_stream(reinterpret_cast<const uint4*>(a.p) + vidx);
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    uint4* ev = reinterpret_cast<uint4*>(a.ema[k]) + vidx;
+    const uint4 re = ld_stream(ev);
+    uint4 we = re;
+#pragma unroll
+    for (int c = 0; c < Tr::CH; ++c) {
+      float p[4], e[4];
+      Tr::unpack4(rp, c, p);
+      Tr::unpack4(re, c, e);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) e[j] = __fmul_rn(e[j], a.s.rate[k]);
+      Tr::rnd4(e);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) e[j] = __fmaf_rn(a.s.alpha[k], p[j], e[j]);
+      Tr::rnd4_store_only(e, we, c);
+    }
+    st_stream(ev, Tr::merge(we, re, rem));
+  }
 }
 
 // Work distribution.  A work item is one *chunk*: kThreads consecutive 16-byte
@@ -854,10 +995,13 @@ __device__ __forceinline__ void update_chunks(const UpdateArgs<T, K>& a, int wor
     float acc = 0.f;
     bool aborted = false;
     const int v = threadIdx.x;
-    if (v < nfull)
-      aborted = update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc, frozen);
+    if (frozen) {                                    // block-uniform: the whole tile belongs to one tensor
+      if (v < nfull) frozen_vector<T, K>(a, vbase + v, VE);
+      else if (v == nfull && len > nfull * VE) frozen_vector<T, K>(a, vbase + v, len - nfull * VE);
+    } else if (v < nfull)
+      aborted = update_vector<T, K, GM, true>(a, vbase + v, VE, coef, acc);
     else if (v == nfull && len > nfull * VE)        // ragged end of a tensor: one masked vector
-      aborted = update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc, frozen);
+      aborted = update_vector<T, K, GM, false>(a, vbase + v, len - nfull * VE, coef, acc);
 
     // block sum, fixed order, one barrier per item (the exchange buffer alternates)
 #pragma unroll

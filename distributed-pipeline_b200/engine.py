@@ -71,6 +71,7 @@ class Engine:
         self._bound: List[torch.Tensor] = []
         self.world_size = 1
         self.nvls = False
+        self.sharded = False
         self._results = None
         self._seg_norms = None
 
@@ -144,6 +145,32 @@ class Engine:
         _lib.check(self.lib.dpk_bind_nvls(self._h, mc_grads, peers, mc_sig, sig.data_ptr(), n_slots))
         self._nvls = (hdl, hsig, sig)  # keep the mappings alive
         self.nvls = True
+
+    def enable_shard(self, params: torch.Tensor, group=None):
+        """Sharded update (dpk_shard_update): map the (symmetric) parameter buffer on the NVSwitch.
+        Collective; after enable_nvls."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        if params.data_ptr() != self._bound[0].data_ptr():
+            raise ValueError("enable_shard: not the bound parameter buffer")
+        hdl = symm_mem.rendezvous(params, group)
+        if not hdl.multicast_ptr:
+            raise RuntimeError("enable_shard: no NVSwitch multicast support on this system")
+        mc = hdl.multicast_ptr + (params.data_ptr() - hdl.buffer_ptrs[hdl.rank])
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group)
+        _lib.check(self.lib.dpk_bind_shard(self._h, mc))
+        self._shard = hdl
+        self.sharded = True
+
+    def shard_update(self, lr: float, weight_decay: float, adam_step: int, inv_scale: float = 1.0, stream=None):
+        _lib.check(self.lib.dpk_shard_update(self._h, lr, weight_decay, adam_step, inv_scale,
+                                             _stream_ptr(stream, self.device)))
+
+    def shard_gather(self, stream=None):
+        """Make exp_avg, exp_avg_sq and the EMA copies complete on every rank again (no-op if they are)."""
+        _lib.check(self.lib.dpk_shard_gather(self._h, _stream_ptr(stream, self.device)))
 
     def enable_nvls_agreed(self, flat, group=None, n_slots: int = 65536):
         """Switch the gradient all-reduce to the library's symmetric-memory kernels only if EVERY
@@ -237,6 +264,10 @@ class Engine:
         """Any world size >= 2: all-reduce and update as one kernel (see dpk_reduce_update)."""
         _lib.check(self.lib.dpk_reduce_update(self._h, lr, weight_decay, adam_step, inv_scale,
                                               _stream_ptr(stream, self.device)))
+
+    def reduce_norm(self, inv_scale: float = 1.0, max_norm: float = 0.0, stream=None):
+        """Any world size >= 2: all-reduce and the norm pass together (see dpk_reduce_norm)."""
+        _lib.check(self.lib.dpk_reduce_norm(self._h, inv_scale, max_norm, _stream_ptr(stream, self.device)))
 
     @property
     def results(self) -> torch.Tensor:

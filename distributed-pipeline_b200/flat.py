@@ -73,7 +73,8 @@ class FlatState:
     policy (``utils/trainer.py:203-207``).
     """
 
-    def __init__(self, parameters: Sequence[torch.nn.Parameter], n_ema: int, symmetric_grads: bool = False):
+    def __init__(self, parameters: Sequence[torch.nn.Parameter], n_ema: int, symmetric_grads: bool = False,
+                 symmetric_params: bool = False):
         """``symmetric_grads``: allocate the gradient buffer from torch's symmetric
         memory allocator so that it can later be mapped on every rank and bound to
         an NVSwitch multicast address (Engine.enable_nvls); collective on the
@@ -96,6 +97,13 @@ class FlatState:
             return torch.zeros(n, dtype=self.dtype, device=self.device)
 
         self.params = buf()
+        self.symmetric_params = False
+        if symmetric_params:
+            # the sharded update multicasts new parameters into every replica: the buffer must be mappable
+            import torch.distributed._symmetric_memory as symm_mem
+            self.params = symm_mem.empty(n, dtype=self.dtype, device=self.device)
+            self.params.zero_()
+            self.symmetric_params = True
         self.symmetric = False
         self.symmetric_error = None
         if symmetric_grads:

@@ -21,9 +21,16 @@ class FusedAdamW:
     def __init__(self, params: Sequence[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999),
                  eps: float = 1e-8, weight_decay: float = 1e-2, ema_rates: Sequence[float] = (),
                  bucket_cap_mb: float = 128, grad_mode: int = _lib.GRAD_CLIPPED, tile_elems: int = 0,
-                 symmetric_grads: bool = False):
+                 symmetric_grads: bool = False, sharded: bool = False):
+        """``sharded``: ZeRO-1 style update (SURVEY f-4; the reference's own nod to it is the
+        "sharded optimizer" branch of grad_clip, utils/trainer.py:248-250).  Each rank updates every
+        W-th chunk and multicasts the new parameters; moments and EMA copies are owner-only until
+        ``gather_shards()`` (called by ``state_dict``).  Enable after ``engine.init_comm()`` and
+        ``engine.enable_nvls(flat.grads)`` with ``engine.enable_shard(flat.params)``.  No clipping."""
         params = list(params)
-        self.flat = FlatState(params, n_ema=len(ema_rates), symmetric_grads=symmetric_grads)
+        self.sharded = bool(sharded)
+        self.flat = FlatState(params, n_ema=len(ema_rates), symmetric_grads=symmetric_grads or sharded,
+                              symmetric_params=sharded)
         self.engine = Engine(self.flat.layout, self.flat.dtype, self.flat.device, ema_rates, betas, eps,
                              bucket_cap_bytes=int(bucket_cap_mb * 1024 * 1024), tile_elems=tile_elems,
                              frozen=self.flat.frozen)
@@ -79,6 +86,14 @@ class FusedAdamW:
         eng = self.engine
         g = self.param_groups[0]
         n = len(eng.buckets)
+        if self.sharded and eng.sharded:
+            if max_norm > 0 or self.skip_if_nonfinite or self.grad_mode != _lib.GRAD_KEEP:
+                raise ValueError("the sharded update supports neither clipping nor a loss scale nor rewritten gradients")
+            self.step_count += 1
+            eng.shard_update(float(g["lr"]), float(g["weight_decay"]), self.step_count, self.inv_scale)
+            self._clip_pending = False
+            self.ema_done = [True] * len(self.ema_rates)
+            return
         if (eng.world_size >= 2 and eng.nvls and self.fused_reduce and max_norm <= 0
                 and self.grad_mode == _lib.GRAD_KEEP and not self.skip_if_nonfinite):
             # no clipping, gradients not rewritten: exchange and update in ONE kernel -- two ranks
@@ -89,6 +104,11 @@ class FusedAdamW:
             self._clip_pending = False
             self.ema_done = [True] * len(self.ema_rates)
             return
+        if max_norm > 0 and eng.world_size >= 2 and eng.nvls and self.fused_reduce:
+            # clipping: the all-reduce and the norm pass together, then the update
+            eng.reduce_norm(self.inv_scale, float(max_norm))
+            self._clip_pending = True
+            return self.step()
         if eng.world_size >= 4:
             # every gradient is already in place: one "peers complete" barrier serves all buckets
             eng.all_buckets_ready()
@@ -181,7 +201,13 @@ class FusedAdamW:
         return {p: {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
                 for p, m, v, fr in zip(f.param_list, f.exp_avg_views, f.exp_avg_sq_views, f.frozen) if not fr}
 
+    def gather_shards(self):
+        """After sharded steps: complete every rank's moments and EMA copies (collective)."""
+        if self.sharded:
+            self.engine.shard_gather()
+
     def state_dict(self) -> Dict:
+        self.gather_shards()
         f = self.flat
         state = {}
         if self.step_count:

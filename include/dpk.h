@@ -266,6 +266,32 @@ int dpk_reduce_update_pair(dpk_handle* h, double lr, double weight_decay, int64_
 int dpk_reduce_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
                       double inv_scale, void* stream);
 
+/* The clipping counterpart: DDP's all-reduce (utils/trainer.py:118-125) and pass 1
+ * (grad_clip, :246-255) as one kernel for four or more ranks -- the same grid
+ * split, the second part taking the per-tile sums of squares range by range as the
+ * averaged gradient arrives; two ranks run the pair all-reduce with the norm pass
+ * bucket by bucket behind it.  Result block and gradient buffers afterwards are
+ * exactly those of dpk_all_buckets_ready + dpk_wait_allreduce + dpk_grad_norm;
+ * dpk_fused_update(use_clip_coef = 1) follows as usual. */
+int dpk_reduce_norm(dpk_handle* h, double inv_scale, double max_norm, void* stream);
+
+/* ---- sharded update (opt-in).  The reference itself points at it: its grad_clip
+ * keeps a branch for "the sharded optimizer" (utils/trainer.py:248-250).  Instead of
+ * all-reducing the gradient and updating W identical replicas, each rank owns every
+ * W-th 4 KiB chunk: it pulls the switch-reduced gradient of its chunks
+ * (reduce-scatter), runs AdamW + EMA on them from registers and multicasts the new
+ * parameters into every replica (all-gather) -- one kernel, the NVLink volume of one
+ * all-reduce, 1/W of the update's HBM traffic.  Parameters afterwards are
+ * bit-identical to the replica path; exp_avg, exp_avg_sq and the EMA copies are
+ * valid on the owner of each chunk only, until dpk_shard_gather makes every rank's
+ * copies complete again (call it before state_dict / save / reading EMA weights).
+ * No clipping in this mode.  Needs dpk_bind_nvls plus the multicast address of the
+ * (symmetric) parameter buffer. */
+int dpk_bind_shard(dpk_handle* h, void* mc_params);
+int dpk_shard_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
+                     double inv_scale, void* stream);
+int dpk_shard_gather(dpk_handle* h, void* stream);
+
 /* Device address of the result block (DPK_R_COUNT doubles). */
 int dpk_result_ptr(dpk_handle* h, void** d_out);
 /* Copy the result block to `out[DPK_R_COUNT]` and wait for it: the single host

@@ -30,8 +30,11 @@ from oracle.torch_port import ReferenceUpdatePort  # noqa: E402
 
 def port_check(world, rank, dev, dtype):
     """Three steps of the library (selected all-reduce + fused update, clip 1.0) against the reference port fed
-    with ncclAvg gradients.  fp32: relative 1e-6 (W>=4: summation order differs from NCCL's by design);
-    bf16: one bf16 ulp at W=2 (same gradients bit for bit), a few at W>=4 where the switch rounds differently."""
+    with ncclAvg gradients.  fp32: relative 1e-6 where the gradients are the same bits (W=2).  Through the
+    switch every element is the correctly rounded mean while ncclAvg is an ulp off it in a third of them
+    (parity_check reports both counts); Adam's first steps normalise the gradient (m/sqrt(v) ~ +-1), which
+    carries those ulps into the parameters at the 1e-6 level: 5e-6 allowed there.  bf16: one bf16 ulp at
+    W=2, a few where the switch did the additions."""
     shapes = [(257, 33), (7,), (150001,), (64, 64), (3,)]
     torch.manual_seed(11)
     ps = [torch.nn.Parameter((torch.randn(s, device=dev) * 0.02).to(dtype)) for s in shapes]
@@ -58,10 +61,59 @@ def port_check(world, rank, dev, dtype):
         rms = b.pow(2).mean().sqrt()
         worst = max(worst, float(((a - b).abs() / (b.abs() + rms)).max().item()))
     switch = world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1"
-    tol = 1e-6 if dtype == torch.float32 else (2 ** -5 if switch else 2 ** -7)
+    tol = (5e-6 if switch else 1e-6) if dtype == torch.float32 else (2 ** -5 if switch else 2 ** -7)
     assert worst <= tol, f"{dtype} W={world}: parameters/EMA differ from the reference port by {worst:.3e} (> {tol:.1e})"
     opt.engine.close()
     return worst
+
+
+def shard_check(world, rank, dev, dtype):
+    """Sharded (ZeRO-1 style) update against the replica path on the same per-rank gradients: parameters
+    bit-identical on every rank after every step; after gather_shards() both moments and the EMA copies too."""
+    shapes = [(257, 33), (7,), (150001,), (64, 64), (3,), (40000,)]
+
+    def make(sharded):
+        torch.manual_seed(21)
+        ps = [torch.nn.Parameter((torch.randn(s, device=dev) * 0.02).to(dtype)) for s in shapes]
+        o = FusedAdamW(ps, lr=1e-3, weight_decay=0.01, ema_rates=[0.999, 0.9], bucket_cap_mb=0.25,
+                       grad_mode=_lib.GRAD_KEEP, symmetric_grads=True, sharded=sharded)
+        o.engine.init_comm()
+        o.engine.enable_nvls(o.flat.grads)
+        if sharded:
+            o.engine.enable_shard(o.flat.params)
+        return o
+    sh, rep = make(True), make(False)
+    gen = torch.Generator(device=dev).manual_seed(300 + rank)
+    for it in range(3):
+        g = (torch.randn(sh.flat.layout.n_elems, device=dev, generator=gen) * 0.05).to(dtype)
+        sh.flat.grads.copy_(g)
+        rep.flat.grads.copy_(g)
+        sh.reduce_and_step()
+        rep.engine.all_buckets_ready()
+        rep.engine.wait_allreduce()
+        rep.step()
+        torch.cuda.synchronize()
+        assert torch.equal(sh.flat.grads, g), "the sharded pass leaves the local gradient untouched"
+        assert torch.equal(sh.flat.params, rep.flat.params), f"{dtype} W={world} step {it}: sharded parameters differ"
+        a, b = sh.engine.read_results_sync(), rep.engine.read_results_sync()
+        assert abs(a[_lib.R_LOGGED_NORM] - b[_lib.R_LOGGED_NORM]) <= 1e-6 * b[_lib.R_LOGGED_NORM] and a[_lib.R_COMM_TIMEOUT] == 0
+    # owner-only state before the gather, complete state after it
+    assert not torch.equal(sh.flat.exp_avg, rep.flat.exp_avg)
+    sd = sh.state_dict()          # gathers
+    torch.cuda.synchronize()
+    for name, x, y in (("exp_avg", sh.flat.exp_avg, rep.flat.exp_avg), ("exp_avg_sq", sh.flat.exp_avg_sq, rep.flat.exp_avg_sq),
+                       ("ema0", sh.flat.emas[0], rep.flat.emas[0]), ("ema1", sh.flat.emas[1], rep.flat.emas[1])):
+        assert torch.equal(x, y), f"{dtype} W={world}: {name} differs after gather_shards"
+    assert len(sd["state"]) == len(shapes)
+    # and stepping on after a gather keeps working
+    g = (torch.randn(sh.flat.layout.n_elems, device=dev, generator=gen) * 0.05).to(dtype)
+    sh.flat.grads.copy_(g); rep.flat.grads.copy_(g)
+    sh.reduce_and_step()
+    rep.engine.all_buckets_ready(); rep.engine.wait_allreduce(); rep.step()
+    sh.gather_shards()
+    torch.cuda.synchronize()
+    assert torch.equal(sh.flat.params, rep.flat.params) and torch.equal(sh.flat.emas[1], rep.flat.emas[1])
+    sh.engine.close(); rep.engine.close()
 
 
 def sampler_check(world, rank, dev):
@@ -112,6 +164,13 @@ def main():
         w = port_check(world, rank, dev, dtype)
         if rank == 0:
             print(f"reference port, {dtype}, W={world}: worst relative difference {w:.3e}", flush=True)
+    switch = world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1"
+    for dtype in (torch.float32, torch.bfloat16):
+        if dtype == torch.bfloat16 and not switch:
+            continue      # two ranks' replica path averages bf16 pairs exactly; the switch's bf16 add differs (see bench.parity_check)
+        shard_check(world, rank, dev, dtype)
+        if rank == 0:
+            print(f"sharded update, {dtype}, W={world}: bit-identical to the replica path", flush=True)
     sampler_check(world, rank, dev)
     dist.barrier()
     if rank == 0:

@@ -80,6 +80,22 @@ def test_static_norm_matches_handle_norm_on_consecutive_calls():
     assert got[_lib.R_TOTAL_NORM] == 0.0 and got[_lib.R_NONFINITE] == 0.0 and got[_lib.R_CLIP_COEF] == 1.0
 
 
+def test_static_norm_at_its_maximum_size():
+    """Exactly DPK_STATIC_MAX_ELEMS elements: all 65 536 scratch slots in use, nothing refused."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    out = torch.zeros(_lib.R_COUNT, dtype=torch.float64, device=dev)
+    g = torch.full((_lib.STATIC_MAX_ELEMS,), 0.5, dtype=torch.bfloat16, device=dev)   # 1 GiB
+    g[-1] = 3.0
+    got = _static_norm(g, 1.0, 100.0, out)
+    want = _handle_norm(g, 1.0, 100.0)
+    truth = ((_lib.STATIC_MAX_ELEMS - 1) * 0.25 + 9.0) ** 0.5
+    assert got[_lib.R_TOTAL_NORM] == want[_lib.R_TOTAL_NORM] and got[_lib.R_CLIP_COEF] == want[_lib.R_CLIP_COEF]
+    assert abs(got[_lib.R_TOTAL_NORM] - truth) <= 2 ** -7 * truth and got[_lib.R_NONFINITE] == 0.0
+    # and the call after it, a small one, is not disturbed by 65 536 stale partials
+    small = torch.randn(10_000, device=dev)
+    assert _static_norm(small, 1.0, 0.0, out)[_lib.R_TOTAL_NORM] == _handle_norm(small, 1.0, 0.0)[_lib.R_TOTAL_NORM]
+
+
 def test_static_norm_rejects_what_it_cannot_hold():
     lib = _lib.lib()
     dev = torch.device("cuda", torch.cuda.current_device())
