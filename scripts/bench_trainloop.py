@@ -90,7 +90,7 @@ def run(args, ClockSampler):
             ms = float(t.item())
         return ms
 
-    steps = max(2, min(args.steps, 6 if n_micro > 8 else 10))
+    steps = max(2, min(args.steps, 6 if n_micro > 8 else 20))
     warmup = max(3, min(args.warmup, 3))
 
     loop = make_loop()

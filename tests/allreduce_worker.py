@@ -29,41 +29,68 @@ from oracle.torch_port import ReferenceUpdatePort  # noqa: E402
 
 
 def port_check(world, rank, dev, dtype):
-    """Three steps of the library (selected all-reduce + fused update, clip 1.0) against the reference port fed
-    with ncclAvg gradients.  fp32: relative 1e-6 where the gradients are the same bits (W=2).  Through the
-    switch every element is the correctly rounded mean while ncclAvg is an ulp off it in a third of them
-    (parity_check reports both counts); Adam's first steps normalise the gradient (m/sqrt(v) ~ +-1), which
-    carries those ulps into the parameters at the 1e-6 level: 5e-6 allowed there.  bf16: one bf16 ulp at
-    W=2, a few where the switch did the additions."""
+    """Three CLIPPED steps of the library (its all-reduce + norm pass + fused update, clip 1.0, gradients
+    rewritten as clip_grad_norm_ leaves them) against the reference port (oracle/torch_port.py: clip_grad_norm_,
+    AdamW, eager EMA on torch-CUDA).
+
+    (1) The port is fed the SAME averaged gradient the library's all-reduce produces (a second instance runs
+        the bucket all-reduce), so what is compared is everything behind the all-reduce, clipping included:
+        fp32 relative 1e-6, bf16 two bf16 ulps (the bf16 clip coefficient may land one ulp apart).
+    (2) fp32 only: the port fed with ncclAvg gradients instead -- an independent end-to-end check that includes
+        NCCL's own rounding.  Where the gradients are the same bits (W=2 pair exchange) 1e-6.  Through the switch
+        every element is the correctly rounded mean while ncclAvg is an ulp of the largest addend off it in a
+        third to half of them; where the W contributions nearly cancel that is a large relative error of the mean,
+        and Adam's first steps divide by |mean|: measured 1.4e-6 at W=4, 3.4e-5 at W=8.  Gate there: 1e-4.
+        (In bf16 neither NCCL's ring nor the switch yields the rounded mean and the same effect reaches 1e-1:
+        not a meaningful gate, hence (1).)"""
     shapes = [(257, 33), (7,), (150001,), (64, 64), (3,)]
-    torch.manual_seed(11)
-    ps = [torch.nn.Parameter((torch.randn(s, device=dev) * 0.02).to(dtype)) for s in shapes]
-    ref_ps = [torch.nn.Parameter(p.detach().clone()) for p in ps]
-    opt = FusedAdamW(ps, lr=1e-3, weight_decay=0.01, ema_rates=[0.999], bucket_cap_mb=0.25,
-                     grad_mode=_lib.GRAD_CLIPPED, symmetric_grads=True)
-    opt.engine.init_comm()
-    opt.engine.enable_nvls(opt.flat.grads)
-    port = ReferenceUpdatePort(ref_ps, lr=1e-3, ema_rates=[0.999], weight_decay=0.01, gradient_clipping=1.0)
+    switch = world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1"
+
+    def make(mode):
+        torch.manual_seed(11)
+        ps = [torch.nn.Parameter((torch.randn(s, device=dev) * 0.02).to(dtype)) for s in shapes]
+        o = FusedAdamW(ps, lr=1e-3, weight_decay=0.01, ema_rates=[0.999], bucket_cap_mb=0.25, grad_mode=mode,
+                       symmetric_grads=True)
+        o.engine.init_comm()
+        o.engine.enable_nvls(o.flat.grads)
+        return ps, o
+    ps, opt = make(_lib.GRAD_CLIPPED)
+    _, reducer = make(_lib.GRAD_KEEP)                   # only its all-reduce is used
+    ports = {}
+    for feed in (("own", "nccl") if dtype == torch.float32 else ("own",)):
+        rp = [torch.nn.Parameter(p.detach().clone()) for p in ps]
+        ports[feed] = (rp, ReferenceUpdatePort(rp, lr=1e-3, ema_rates=[0.999], weight_decay=0.01, gradient_clipping=1.0))
     gen = torch.Generator(device=dev).manual_seed(900 + rank)
     for _ in range(3):
         g = (torch.randn(opt.flat.layout.n_elems, device=dev, generator=gen) * 0.05).to(dtype)
         opt.flat.grads.copy_(g)
-        avg = g.clone()
-        dist.all_reduce(avg, op=dist.ReduceOp.AVG)
-        for p, gv in zip(ref_ps, opt.flat.layout.views(avg, opt.flat.shapes)):
-            p.grad = gv.clone()
+        reducer.flat.grads.copy_(g)
+        reducer.engine.all_buckets_ready()
+        reducer.engine.wait_allreduce()
+        torch.cuda.synchronize()
+        avg = {"own": reducer.flat.grads.clone(), "nccl": g.clone()}
+        dist.all_reduce(avg["nccl"], op=dist.ReduceOp.AVG)
+        for feed, (rp, port) in ports.items():
+            for p, gv in zip(rp, opt.flat.layout.views(avg[feed], opt.flat.shapes)):
+                p.grad = gv.clone()
+            port.optimize()
         opt.reduce_and_step(1.0)
-        port.optimize()
     torch.cuda.synchronize()
-    worst = 0.0
-    for a, b in list(zip(ps, ref_ps)) + list(zip(opt.flat.ema_views[0], port.ema_params[0])):
-        a, b = a.detach().double(), b.detach().double()
-        rms = b.pow(2).mean().sqrt()
-        worst = max(worst, float(((a - b).abs() / (b.abs() + rms)).max().item()))
-    switch = world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1"
-    tol = (5e-6 if switch else 1e-6) if dtype == torch.float32 else (2 ** -5 if switch else 2 ** -7)
-    assert worst <= tol, f"{dtype} W={world}: parameters/EMA differ from the reference port by {worst:.3e} (> {tol:.1e})"
+    worst = {}
+    for feed, (rp, port) in ports.items():
+        w = 0.0
+        for a_, b_ in list(zip(ps, rp)) + list(zip(opt.flat.ema_views[0], port.ema_params[0])):
+            a_, b_ = a_.detach().double(), b_.detach().double()
+            rms = b_.pow(2).mean().sqrt()
+            w = max(w, float(((a_ - b_).abs() / (b_.abs() + rms)).max().item()))
+        worst[feed] = w
+    tol_own = 1e-6 if dtype == torch.float32 else 2 ** -7
+    assert worst["own"] <= tol_own, f"{dtype} W={world}: differs from the reference port by {worst['own']:.3e} (> {tol_own:.1e})"
+    if "nccl" in worst:
+        tol = 1e-4 if switch else 1e-6
+        assert worst["nccl"] <= tol, f"{dtype} W={world}: differs from the ncclAvg-fed port by {worst['nccl']:.3e} (> {tol:.1e})"
     opt.engine.close()
+    reducer.engine.close()
     return worst
 
 
@@ -163,7 +190,7 @@ def main():
     for dtype in (torch.float32, torch.bfloat16):
         w = port_check(world, rank, dev, dtype)
         if rank == 0:
-            print(f"reference port, {dtype}, W={world}: worst relative difference {w:.3e}", flush=True)
+            print(f"reference port, {dtype}, W={world}: worst relative difference {w}", flush=True)
     switch = world > 2 or os.environ.get("DPK_FORCE_MULTIMEM") == "1"
     for dtype in (torch.float32, torch.bfloat16):
         if dtype == torch.bfloat16 and not switch:
