@@ -159,13 +159,12 @@ struct KernelTimer {
       if (cudaEventCreate(&e) != cudaSuccess) return;
       v.push_back(e);
     }
-    cudaEventRecord(v[need - 2], st);
+    if (cudaEventRecord(v[need - 2], st) != cudaSuccess) return;  // no begin mark: this launch stays untimed
     end = v[need - 1];
   }
   void stop() {
     if (end) {
-      cudaEventRecord(end, st);
-      h->tcount[which]++;
+      if (cudaEventRecord(end, st) == cudaSuccess) h->tcount[which]++;  // a pair counts only if both marks exist
       end = nullptr;
     }
   }

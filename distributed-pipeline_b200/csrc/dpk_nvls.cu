@@ -593,7 +593,10 @@ extern "C" int dpk_bind_nvls(dpk_handle* h, void* mc_grads, void* const* peer_gr
     while ((1ll << shift) < want) ++shift;
     while (((n_vec + (1ll << shift) - 1) >> shift) > h->flag_slots) ++shift;
     h->unit_shift = shift;
-    h->fused_comm_blocks = 32;  // measured at W=8: 32 -> 0.947 ms/step, 64 -> 0.999, 96 -> 1.094
+    // Collective blocks: each holds 32 KiB in flight, and a rank's share of the reduction is S/W, so the
+    // count that saturates the links scales with 1/W.  Measured (ms/step, fp32 DiffuSeq-base): W=8: 16 -> 1.132,
+    // 24 -> 0.972, 32 -> 0.947, 64 -> 0.999, 96 -> 1.094;  W=4: 32 -> 1.094, 64 -> 0.928.
+    h->fused_comm_blocks = std::max(16, std::min(128, 256 / std::max(h->world, 1)));
     if (const char* e = getenv("DPK_FUSED_COMM_BLOCKS")) h->fused_comm_blocks = std::max(1, atoi(e));
     h->fused_update_blocks = 0;
     if (const char* e = getenv("DPK_FUSED_UPDATE_BLOCKS")) h->fused_update_blocks = std::max(1, atoi(e));

@@ -12,7 +12,5 @@ if [ "$N" = 8 ]; then
 else
   tr bench.py --gpus $N --steps 100 --warmup 10 > $O/r02j_n${N}_default.log 2>&1; echo "default rc=$?"
   tr bench.py --gpus $N --steps 100 --warmup 10 --no-e2e --no-parity --workload diffuseq-base-bf16-ema2-clip > $O/r02j_n${N}_bf16clip.log 2>&1; echo "bf16clip rc=$?"
-  tr bench.py --gpus $N --steps 100 --warmup 10 --sharded --no-parity > $O/r02j_n${N}_sharded.log 2>&1; echo "sharded rc=$?"
-  T=300 tr bench.py --gpus $N --workload trainloop-bf16-ema2-clip --steps 10 --warmup 3 > $O/r02j_n${N}_trainloop.log 2>&1; echo "trainloop rc=$?"
 fi
 grep -h '^{' $O/r02j_n${N}_*.log | cut -c1-200

@@ -192,3 +192,56 @@ def test_fused_adamw_state_dict_is_torch_adamw_layout(monkeypatch):
         ours.zero_grad(set_to_none=True)
     with pytest.raises(NotImplementedError):
         ours.step(closure=lambda: None)
+
+
+def test_round2_host_logic(monkeypatch):
+    """Layout / reducer / logger / dist_util details fixed in round 2, all without a GPU."""
+    # a trailing zero-element tensor sits at offset == n_elems: it belongs to the range that ends there
+    lay = FlatLayout.from_numels([100, 7, 0], 4)
+    assert lay.offsets[2] == lay.n_elems
+    assert lay.segment_of(0, lay.n_elems) == [0, 1, 2]
+    assert lay.segment_of(0, lay.offsets[1]) == [0]
+    # running mean of n equal samples in one update == n single updates
+    a, b = logger.Logger(None), logger.Logger(None)
+    a.logkv_mean("x", 1.0)
+    b.logkv_mean("x", 1.0)
+    for _ in range(5):
+        a.logkv_mean("x", 3.5)
+    b.logkv_mean_n("x", 3.5, 5)
+    assert abs(a.name2val["x"] - b.name2val["x"]) < 1e-12 and a.name2cnt["x"] == b.name2cnt["x"] == 6
+    # LOCAL_RANK alone decides, as in the reference (basic_utils/dist_util.py:66): with the other env://
+    # variables missing init_process_group fails and setup_dist falls back to a single process
+    monkeypatch.setenv("LOCAL_RANK", "0")
+    for k in ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        monkeypatch.delenv(k, raising=False)
+    monkeypatch.setitem(dist_util._state, "setup_done", None)
+    assert dist_util.setup_dist(silent=True) is False
+    assert dist_util.get_world_size() == 1
+    # the new constructor keywords are optional and keyword-only
+    sig = inspect.signature(TrainLoop.__init__)
+    for k in ("schedule_sampler", "diffusion_steps", "timestep_key", "use_fp16", "grads_after_step", "grad_allreduce"):
+        assert sig.parameters[k].kind is inspect.Parameter.KEYWORD_ONLY
+    assert sig.parameters["schedule_sampler"].default is None
+
+
+def test_reducer_waits_only_for_parameters_that_get_gradients():
+    """A frozen tensor never fires a hook: it must not hold its bucket (and every later one) back."""
+    from distributed_pipeline_b200.reducer import BucketReducer
+
+    class FakeFlat:
+        pass
+
+    class FakeEngine:
+        world_size = 2
+        buckets = [(300, 100), (0, 300)]          # tail first
+
+    ps = [torch.nn.Parameter(torch.zeros(100)), torch.nn.Parameter(torch.zeros(200), requires_grad=False),
+          torch.nn.Parameter(torch.zeros(100))]
+    flat = FakeFlat()
+    flat.param_list = ps
+    flat.layout = FlatLayout((0, 100, 300), (100, 200, 100), 400, 4)
+    r = BucketReducer(flat, FakeEngine())
+    assert r.bucket_params == [[2], [0, 1]]
+    assert r._hooked == [1, 1] and r._pending == [1, 1] and r._ready == [False, False]
+    assert len(r._handles) == 2                   # no hook on the frozen tensor
+    r.remove()
