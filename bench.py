@@ -549,6 +549,9 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # a benchmark has no eval callbacks that could legitimately hold a rank back for minutes: a peer that does
+    # not show up within a minute is gone, fail instead of parking the GPUs for the library's ten-minute default
+    os.environ.setdefault("DPK_PEER_TIMEOUT_MS", "60000")
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             sys.exit("launch with torch.distributed.run --nproc-per-node N for --gpus N > 1")

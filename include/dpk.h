@@ -286,7 +286,11 @@ int dpk_reduce_norm(dpk_handle* h, double inv_scale, double max_norm, void* stre
  * valid on the owner of each chunk only, until dpk_shard_gather makes every rank's
  * copies complete again (call it before state_dict / save / reading EMA weights).
  * No clipping in this mode.  Needs dpk_bind_nvls plus the multicast address of the
- * (symmetric) parameter buffer. */
+ * (symmetric) parameter buffer.  dpk_shard_update and dpk_shard_gather issue small
+ * NCCL collectives on the CALLER's stream: do not run them while bucket all-reduces
+ * of the same handle are still in flight on the library's communication stream (one
+ * communicator serves one stream at a time) -- in this mode there are none, the
+ * gradient exchange lives inside dpk_shard_update. */
 int dpk_bind_shard(dpk_handle* h, void* mc_params);
 int dpk_shard_update(dpk_handle* h, double lr, double weight_decay, int64_t adam_step,
                      double inv_scale, void* stream);
