@@ -197,6 +197,7 @@ class FusedAdamW:
     def state(self) -> Dict[torch.nn.Parameter, Dict[str, torch.Tensor]]:
         if self.step_count == 0:
             return {}
+        self.gather_shards()
         f = self.flat
         return {p: {"step": torch.tensor(float(self.step_count)), "exp_avg": m, "exp_avg_sq": v}
                 for p, m, v, fr in zip(f.param_list, f.exp_avg_views, f.exp_avg_sq_views, f.frozen) if not fr}

@@ -70,3 +70,18 @@ def test_ddp_style_allreduce_is_what_torch_ddp_computes():
     for a, b in zip(gs, want):
         assert torch.allclose(a, b, rtol=1e-6)
     assert FakeDist.calls == [14, 35]      # last tensors first; a bucket closes once it reaches the cap
+
+
+def test_ordered_bits_counts_ulps():
+    """bench.parity_check's ulp distance: consecutive floats differ by one, across zero too."""
+    import torch
+    sys.path.insert(0, ROOT)
+    import bench
+    x = torch.tensor([1.0, -1.0, 0.0, 1e-30], dtype=torch.float32)
+    up = torch.nextafter(x, torch.full_like(x, float("inf")))
+    assert (bench._ordered_bits(up) - bench._ordered_bits(x)).tolist() == [1, 1, 1, 1]
+    assert int(bench._ordered_bits(torch.tensor([-0.0])).item()) == int(bench._ordered_bits(torch.tensor([0.0])).item()) == 0
+    b = torch.tensor([1.0, -2.5], dtype=torch.bfloat16)
+    nb = (b.view(torch.int16) + 1).view(torch.bfloat16)          # next bf16 away from zero
+    assert (bench._ordered_bits(nb) - bench._ordered_bits(b)).abs().tolist() == [1, 1]
+    assert bench.bytes_per_param("f32", 1, -1.0, "keep") == 36 and bench.bytes_per_param("bf16", 2, 1.0, "keep") == 24
